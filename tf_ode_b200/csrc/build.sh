@@ -1,0 +1,9 @@
+#!/bin/bash
+# Builds the C-ABI shared library for sm_100a, in-tree (the .so travels to the GPU box with the snapshot).
+set -e
+cd "$(dirname "$0")"
+NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
+$NVCC -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
+  -Xcompiler -fPIC -shared -cudart static ${TFODE_NVCC_EXTRA} \
+  -o libtfode_b200.so tfode_capi.cu
+echo "built $(pwd)/libtfode_b200.so"

@@ -1,0 +1,478 @@
+// C ABI of the batched rover stepping engine (include/tfode_batch.h) and the host-side
+// model tables.  No CPU stepping path exists here: every compute entry point launches the
+// sm_100a kernels and fails with TFODE_ECUDA when no device is usable.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "tfode_kernels.cuh"
+#include "tfode_policy_tc.cuh"
+
+using namespace tfode;
+
+static thread_local std::string g_create_error;
+
+struct TfodeBatch {
+  TfodeBatchConfig cfg;
+  StepParams P;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int64_t launches = 0;
+  // device buffers
+  EnvRec* rec = nullptr; int* budget = nullptr;
+  float* hf_h = nullptr; float* hf_bmax = nullptr;
+  float* policy_in = nullptr; int* parked_list = nullptr; int* n_parked = nullptr;
+  float* trans = nullptr; int* n_trans = nullptr; int trans_cap = 0;
+  float* ext_speed = nullptr;
+  float* weights = nullptr;   // fp32 W1 b1 W2 b2 W3 b3
+  PolicyTC tc;                // bf16 operand copies for the tcgen05 path
+  bool has_policy = false;
+  // staging for the host round trip
+  float* d_obs = nullptr; float* d_rew = nullptr; uint8_t* d_done = nullptr; float* d_act = nullptr;
+  float* h_pin = nullptr; size_t h_pin_bytes = 0;
+  int* d_ids = nullptr; int ids_cap = 0;
+  size_t smem_bytes = 0;
+};
+
+#define CK(call)                                                                            \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      b->err = std::string(#call) + ": " + cudaGetErrorString(e_);                          \
+      return TFODE_ECUDA;                                                                   \
+    }                                                                                       \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// The rover as tables (restates the constructor of src/rover_1.cc:49-233, ode/wheel.hh:56-74,
+// ode/box.hh:54-62, ode/ft_sensor.cc:50-55 and the step boxes of src/rover_training_1.cc:88-98).
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct BodySpec { double x, y, z, mass, lx, ly, lz; int cyl; };  // cyl: dMassSetCylinderTotal(axis z, r=lx, l=lz)
+
+void build_model(Model& M) {
+  std::memset(&M, 0, sizeof(M));
+  const double wheelbase = 0.58, wheeltrack = 0.61, wheel_r = 0.105, wheel_w = 0.1, belly = 0.33;
+  const double front_len = 0.345, front_h = 0.225, front_w = 0.200;
+  const double fx = front_len / 2 - 0.063, fy = 0.023, fz = belly + front_h / 2;
+  const double rear_len = 0.312, rear_h = 0.177, rear_w = 0.126;
+  const double rx = -rear_len / 2 + 0.046, ry = -0.040, rz = belly + rear_h / 2;
+  const double sea_elev = belly + 0.12;
+  const double boggie_h = sea_elev - belly;
+  const double fork_elev = belly - 0.1 / 2;
+  const double rim_r = wheel_r - wheel_w / 2;
+  const float step_h = (float)(0.105 * 2);
+  const BodySpec bs[NB] = {
+      {fx, fy, fz, 5.25, front_len, front_w, front_h, 0},
+      {0.285, 0, belly + 0.155, 3, 0.0975, 0.151, 0.065, 0},
+      {rx, ry, rz, 3.67, rear_len, rear_w, rear_h, 0},
+      {-wheelbase / 2 + 0.035, 0, belly + boggie_h / 2, 1, 0.1, 0.1, boggie_h, 0},
+      {wheelbase / 2, 0, fork_elev, 1, 0.05, 0.3, 0.1, 0},
+      {-wheelbase / 2, 0, fork_elev, 1, 0.05, 0.3, 0.1, 0},
+      {wheelbase / 2, wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
+      {wheelbase / 2, -wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
+      {-wheelbase / 2, wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
+      {-wheelbase / 2, -wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
+      {1, 0, step_h / 2, 1, 1, 3, step_h, 0},
+      {2, 0, step_h / 2, 1, 2, 3, step_h, 0}};
+  const double s2 = std::sqrt(0.5);
+  for (int b = 0; b < NB; b++) {
+    const BodySpec& s = bs[b];
+    double I[3];
+    if (s.cyl) { double r2 = s.lx * s.lx; I[0] = I[1] = s.mass * (0.25 * r2 + s.lz * s.lz / 12.0); I[2] = s.mass * 0.5 * r2; }
+    else { I[0] = s.mass / 12.0 * (s.ly * s.ly + s.lz * s.lz); I[1] = s.mass / 12.0 * (s.lx * s.lx + s.lz * s.lz); I[2] = s.mass / 12.0 * (s.lx * s.lx + s.ly * s.ly); }
+    M.mass[b] = (float)s.mass; M.invMass[b] = (float)(1.0 / s.mass);
+    for (int k = 0; k < 3; k++) { M.Ib[b][k] = (float)I[k]; M.invIb[b][k] = (float)(1.0 / I[k]); }
+    M.pos0[b][0] = (float)s.x; M.pos0[b][1] = (float)s.y; M.pos0[b][2] = (float)s.z;
+    // wheels: dRFromEulerAngles(pi/2,0,0) = rows (1,0,0),(0,0,1),(0,-1,0) -> quaternion (sqrt(1/2), -sqrt(1/2), 0, 0)
+    M.quat0[b][0] = s.cyl ? (float)s2 : 1.0f; M.quat0[b][1] = s.cyl ? (float)-s2 : 0.0f;
+  }
+  M.step_side[0][0] = 1; M.step_side[0][1] = 3; M.step_side[0][2] = step_h;
+  M.step_side[1][0] = 2; M.step_side[1][1] = 3; M.step_side[1][2] = step_h;
+  // joints: body frames are the world frame for every rover body except the wheels (R_w^T v = (v.x, -v.z, v.y))
+  auto P = [&](int b, int k) { return k == 0 ? bs[b].x : (k == 1 ? bs[b].y : bs[b].z); };
+  auto set_hinge = [&](int j, int b1, int b2, const double* anchor, const double* axis, bool b2_is_wheel) {
+    M.jb1[j] = b1; M.jb2[j] = b2; M.jslider[j] = 0;
+    for (int k = 0; k < 3; k++) { M.anchor1[j][k] = (float)(anchor[k] - P(b1, k)); M.axis1[j][k] = (float)axis[k]; }
+    double d[3] = {anchor[0] - P(b2, 0), anchor[1] - P(b2, 1), anchor[2] - P(b2, 2)};
+    if (b2_is_wheel) {
+      M.anchor2[j][0] = (float)d[0]; M.anchor2[j][1] = (float)-d[2]; M.anchor2[j][2] = (float)d[1];
+      M.axis2[j][0] = (float)axis[0]; M.axis2[j][1] = (float)-axis[2]; M.axis2[j][2] = (float)axis[1];
+      M.qrel[j][0] = (float)s2; M.qrel[j][1] = (float)-s2;
+    } else {
+      for (int k = 0; k < 3; k++) { M.anchor2[j][k] = (float)d[k]; M.axis2[j][k] = (float)axis[k]; }
+      M.qrel[j][0] = 1;
+    }
+    M.lostop[j] = -INFINITY; M.histop[j] = INFINITY;
+  };
+  // 0: battery clamp slider (battery, main), axis y, lo = hi = 0
+  M.jb1[0] = 1; M.jb2[0] = 0; M.jslider[0] = 1; M.axis1[0][1] = 1; M.qrel[0][0] = 1;
+  for (int k = 0; k < 3; k++) M.offset[0][k] = (float)(P(1, k) - P(0, k));
+  { const double a[3] = {0, 0, (fz + rz) / 2}, ax[3] = {0, 0, 1}; set_hinge(1, 2, 0, a, ax, false); }  // centre hinge servo
+  { const double a[3] = {-wheelbase / 2, 0, sea_elev}, ax[3] = {1, 0, 0}; set_hinge(2, 3, 2, a, ax, false);  // boggie hinge, stops +-45 deg
+    M.lostop[2] = (float)(-45 * 0.017453292519943295); M.histop[2] = (float)(45 * 0.017453292519943295); }
+  for (int i = 0; i < 4; i++) {
+    const double a[3] = {P(6 + i, 0), P(6 + i, 1), P(6 + i, 2)}, ax[3] = {0, -1, 0};
+    set_hinge(3 + i, P(6 + i, 0) > 0 ? 4 : 5, 6 + i, a, ax, true);
+  }
+  for (int s = 0; s < 2; s++) { M.jb1[7 + s] = 10 + s; M.jb2[7 + s] = 15; M.jslider[7 + s] = 1; M.axis1[7 + s][2] = 1; }  // Object::fix
+  // geoms
+  for (int k = 0; k < 50; k++) { M.ring[k][0] = (float)(rim_r * std::cos(k * 2 * M_PI / 50)); M.ring[k][1] = (float)(rim_r * std::sin(k * 2 * M_PI / 50)); }
+  M.sphere_r = (float)(wheel_w / 2);
+  for (int g = 0; g < 3; g++) { M.ns_type[g] = 1; M.ns_body[g] = g; M.ns_dim[g][0] = (float)bs[g].lx; M.ns_dim[g][1] = (float)bs[g].ly; M.ns_dim[g][2] = (float)bs[g].lz; }
+  for (int g = 0; g < 4; g++) {  // motor bulks on the forks
+    const int body = 4 + g / 2; const double sy = (g % 2 == 0) ? 1 : -1;
+    M.ns_type[3 + g] = 2; M.ns_body[3 + g] = body; M.ns_rot[3 + g] = 1; M.ns_cb[3 + g] = 1;
+    M.ns_dim[3 + g][0] = 0.025f; M.ns_dim[3 + g][1] = 0.1f;
+    const double ap[3] = {bs[body].x, sy * (wheeltrack - wheel_w - 0.1) / 2, wheel_r};
+    for (int k = 0; k < 3; k++) M.ns_off[3 + g][k] = (float)(ap[k] - P(body, k));
+  }
+  for (int g = 0; g < 4; g++) { M.ns_type[7 + g] = 2; M.ns_body[7 + g] = 6 + g; M.ns_dim[7 + g][0] = (float)rim_r; M.ns_dim[7 + g][1] = (float)wheel_w; }
+  // FT sensors: centre (+-wheelbase/2, 0, belly); A = main / boggie, B = forks
+  for (int s = 0; s < 2; s++) {
+    const double c[3] = {(s == 0 ? 1 : -1) * wheelbase / 2, 0, belly};
+    const int A = s == 0 ? 0 : 3, B = s == 0 ? 4 : 5;
+    for (int k = 0; k < 3; k++) { M.ft_ocA[s][k] = (float)(c[k] - P(A, k)); M.ft_ocB[s][k] = (float)(c[k] - P(B, k)); }
+  }
+  M.getpos_rel[0] = (float)-fx; M.getpos_rel[1] = (float)-fy; M.getpos_rel[2] = (float)(-fz + sea_elev);
+  M.robot_max_speed = (float)std::fmin(7.4351 / wheel_r, 7.4351 * wheel_r);  // Q4
+  // LP_second_order_bilinear(Te = 0.001f, w0 = 4 pi, Q = 0.5f), Filters/cpp/filters.cc:148-158
+  { const float Te = 0.001f; const double w0 = 4 * M_PI; const float Q = 0.5f;
+    double w2T2 = std::pow(w0 * Te, 2), den = 2 * w0 * Te + 4 * Q + Q * w2T2;
+    M.filt_c[0] = 2 * Q * (4 - w2T2) / den; M.filt_c[1] = (2 * w0 * Te - 4 * Q - Q * w2T2) / den; M.filt_c[2] = Q * w2T2 / den; }
+}
+
+int launch_blocks(int n) { return (n + WARPS_PER_CTA - 1) / WARPS_PER_CTA; }
+}  // namespace
+
+extern "C" {
+
+int tfode_batch_config_default(TfodeBatchConfig* c, int preset) {
+  if (!c) return TFODE_EINVAL;
+  std::memset(c, 0, sizeof(*c));
+  c->abi_version = TFODE_ABI_VERSION; c->n_envs = 1; c->scene = TFODE_SCENE_STEP_BOXES; c->controller = TFODE_CTRL_EXTERNAL;
+  c->policy_precision = TFODE_POLICY_FP32; c->auto_reset = 1;
+  c->mu = 0.5f; c->dt = 0.001f; c->erp = 0.2f; c->cfm = 1e-10f; c->pgs_iters = 20; c->sor_w = 1.3f;
+  c->crawling_mode = 1; c->ic_period = 0; c->ic_initially_active = 0;
+  c->speedf = 0.04f; c->term = 0.5f; c->ic_start = -1.0f; c->timeout = 60; c->x_goal = 2.0f; c->y_max = 0.5f;
+  c->x_goal_abs = 1; c->check_upside_down = 1; c->terminate = 0;
+  c->crawler_amp = 30; c->crawler_dt_torque = 2; c->crawler_rate = 10;
+  c->hf_length = 3; c->hf_width = 3;
+  c->seed = 20260411ull; c->max_contacts = 32;
+  switch (preset) {
+    case 0: break;
+    case 1: c->controller = TFODE_CTRL_RANDOM; c->ic_period = 0.5f; c->ic_start = 1.0f; c->x_goal = 1.0f; c->y_max = 0.6f; c->terminate = 1; break;
+    case 2: c->controller = TFODE_CTRL_MLP; c->ic_period = 0.5f; c->ic_start = 1.0f; c->ic_start_jitter = 0.25f; c->exploration = 1; c->fork_callback = 1;
+            c->x_goal = 1.5f; c->y_max = 0.6f; c->terminate = 1; c->step_yaw_jitter_deg = 5.0f; break;
+    case 3: c->scene = TFODE_SCENE_PLANE; c->controller = TFODE_CTRL_CRAWLER; c->mu = 0.6f; c->ic_initially_active = 1; c->term = 0;
+            c->x_goal = 10; c->y_max = 0; c->x_goal_abs = 0; c->check_upside_down = 0; c->terminate = 1; break;
+    default: return TFODE_EINVAL;
+  }
+  return TFODE_OK;
+}
+
+const char* tfode_last_error(const TfodeBatch* b) { return b ? b->err.c_str() : g_create_error.c_str(); }
+int tfode_sizeof_config() { return (int)sizeof(TfodeBatchConfig); }
+int tfode_sizeof_state() { return (int)sizeof(TfodeEnvState); }
+int tfode_sizeof_record() { return (int)sizeof(EnvRec); }
+
+static int launch_reset(TfodeBatch* b, const int* d_ids, int n, int first) {
+  reset_kernel<<<launch_blocks(n), WARPS_PER_CTA * 32, b->smem_bytes, b->stream>>>(b->P, d_ids, n, first);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
+  if (!cfg || !out) { g_create_error = "null argument"; return TFODE_EINVAL; }
+  *out = nullptr;
+  if (cfg->abi_version != TFODE_ABI_VERSION) { g_create_error = "abi_version mismatch"; return TFODE_EINVAL; }
+  if (cfg->n_envs <= 0) { g_create_error = "n_envs must be positive"; return TFODE_EINVAL; }
+  if (cfg->scene < 0 || cfg->scene > 2 || cfg->controller < 0 || cfg->controller > 3) { g_create_error = "bad scene/controller"; return TFODE_EINVAL; }
+  if (cfg->scene == TFODE_SCENE_HEIGHTFIELD && (!cfg->hf_heights || cfg->hf_ncol < 2 || cfg->hf_nrow < 2)) { g_create_error = "heightfield scene without heights"; return TFODE_EINVAL; }
+  if (!(cfg->dt > 0) || cfg->pgs_iters < 1 || cfg->pgs_iters > 1000) { g_create_error = "bad dt / pgs_iters"; return TFODE_EINVAL; }
+  if (std::fabs(cfg->step_yaw_deg) + std::fabs(cfg->step_yaw_jitter_deg) >= 119.0f) { g_create_error = "step yaw must stay below 119 degrees"; return TFODE_EINVAL; }
+  TfodeBatch* b = new TfodeBatch();
+  b->cfg = *cfg;
+  auto fail = [&](int code) { g_create_error = b->err; tfode_batch_destroy(b); return code; };
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { b->err = std::string(#call) + ": " + cudaGetErrorString(e_); return fail(TFODE_ECUDA); } } while (0)
+  CKC(cudaSetDevice(cfg->device));
+  cudaDeviceProp prop; CKC(cudaGetDeviceProperties(&prop, cfg->device));
+  if (prop.major < 10) { b->err = "this engine is built for sm_100a (B200) only"; return fail(TFODE_ECUDA); }
+  const int n = cfg->n_envs;
+  Model M; build_model(M);
+  CKC(cudaMemcpyToSymbol(g_model, &M, sizeof(M)));
+  CKC(cudaMalloc(&b->rec, sizeof(EnvRec) * (size_t)n));
+  CKC(cudaMalloc(&b->budget, sizeof(int) * (size_t)n));
+  CKC(cudaMemset(b->budget, 0, sizeof(int) * (size_t)n));
+  CKC(cudaMalloc(&b->policy_in, sizeof(float) * 17 * (size_t)n));
+  CKC(cudaMalloc(&b->parked_list, sizeof(int) * (size_t)n));
+  CKC(cudaMalloc(&b->n_parked, sizeof(int) * 4));
+  CKC(cudaMemset(b->n_parked, 0, sizeof(int) * 4));
+  b->n_trans = b->n_parked + 1;
+  b->trans_cap = cfg->transition_capacity > 0 ? cfg->transition_capacity : 4 * n;
+  CKC(cudaMalloc(&b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)b->trans_cap));
+  CKC(cudaMalloc(&b->ext_speed, sizeof(float) * (size_t)n));
+  CKC(cudaMalloc(&b->d_obs, sizeof(float) * 17 * (size_t)n));
+  CKC(cudaMalloc(&b->d_rew, sizeof(float) * (size_t)n));
+  CKC(cudaMalloc(&b->d_done, (size_t)n));
+  CKC(cudaMalloc(&b->d_act, sizeof(float) * 2 * (size_t)n));
+  b->h_pin_bytes = sizeof(float) * (17 + 1 + 2) * (size_t)n + (size_t)n + 64;
+  CKC(cudaMallocHost(&b->h_pin, b->h_pin_bytes));
+  StepParams& P = b->P;
+  std::memset(&P, 0, sizeof(P));
+  P.rec = b->rec; P.budget = b->budget; P.n_envs = n; P.set_budget = -1; P.cfg = *cfg; P.cfg.hf_heights = nullptr;
+  P.policy_in = b->policy_in; P.parked_list = b->parked_list; P.n_parked = b->n_parked;
+  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.ext_speed = nullptr;
+  if (cfg->scene == TFODE_SCENE_HEIGHTFIELD) {
+    const int nc = cfg->hf_ncol, nr = cfg->hf_nrow;
+    const int nbx = (nc + 7) / 8, nbz = (nr + 7) / 8;
+    std::vector<float> bm((size_t)nbx * nbz, -1e30f);
+    float hmax = -1e30f;
+    for (int iz = 0; iz < nr; iz++) for (int ix = 0; ix < nc; ix++) {
+      float v = cfg->hf_heights[(size_t)iz * nc + ix];
+      if (!(v == v)) { b->err = "NaN in heightfield"; return fail(TFODE_EINVAL); }
+      hmax = std::fmax(hmax, v);
+      float& m = bm[(size_t)(iz / 8) * nbx + ix / 8]; m = std::fmax(m, v);
+    }
+    CKC(cudaMalloc(&b->hf_h, sizeof(float) * (size_t)nc * nr));
+    CKC(cudaMemcpy(b->hf_h, cfg->hf_heights, sizeof(float) * (size_t)nc * nr, cudaMemcpyHostToDevice));
+    CKC(cudaMalloc(&b->hf_bmax, sizeof(float) * bm.size()));
+    CKC(cudaMemcpy(b->hf_bmax, bm.data(), sizeof(float) * bm.size(), cudaMemcpyHostToDevice));
+    HfParams& H = P.hf;
+    H.h = b->hf_h; H.blockmax = b->hf_bmax; H.ncol = nc; H.nrow = nr; H.nbx = nbx; H.nbz = nbz;
+    H.sx = (float)((double)cfg->hf_length / (nc - 1)); H.sz = (float)((double)cfg->hf_width / (nr - 1));
+    H.inv_sx = (float)((nc - 1) / (double)cfg->hf_length); H.inv_sz = (float)((nr - 1) / (double)cfg->hf_width);
+    H.length = cfg->hf_length; H.width = cfg->hf_width; H.hmax = hmax;
+    for (int k = 0; k < 3; k++) H.pos[k] = cfg->hf_pos[k];
+  }
+  b->cfg.hf_heights = nullptr;
+  b->smem_bytes = sizeof(WarpSm) * WARPS_PER_CTA;
+  CKC(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
+  CKC(cudaFuncSetAttribute(reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
+  if (launch_reset(b, nullptr, n, 1) != TFODE_OK) return fail(TFODE_ECUDA);
+  CKC(cudaStreamSynchronize(b->stream));
+  *out = b;
+  return TFODE_OK;
+#undef CKC
+}
+
+void tfode_batch_destroy(TfodeBatch* b) {
+  if (!b) return;
+  cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
+  cudaFree(b->n_parked); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
+  cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
+  policy_tc_free(b->tc);
+  if (b->h_pin) cudaFreeHost(b->h_pin);
+  delete b;
+}
+
+int tfode_batch_set_stream(TfodeBatch* b, void* stream) { if (!b) return TFODE_EINVAL; b->stream = (cudaStream_t)stream; return TFODE_OK; }
+int tfode_batch_n_envs(const TfodeBatch* b) { return b ? b->cfg.n_envs : 0; }
+int64_t tfode_batch_launch_count(const TfodeBatch* b) { return b ? b->launches : 0; }
+int tfode_batch_sync(TfodeBatch* b) { if (!b) return TFODE_EINVAL; CK(cudaStreamSynchronize(b->stream)); return TFODE_OK; }
+
+int tfode_batch_reset(TfodeBatch* b, const int32_t* env_ids, int n) {
+  if (!b) return TFODE_EINVAL;
+  if (!env_ids) return launch_reset(b, nullptr, b->cfg.n_envs, 0);
+  if (n <= 0) return TFODE_OK;
+  for (int i = 0; i < n; i++) if (env_ids[i] < 0 || env_ids[i] >= b->cfg.n_envs) { b->err = "env id out of range"; return TFODE_EINVAL; }
+  if (n > b->ids_cap) { cudaFree(b->d_ids); b->d_ids = nullptr; CK(cudaMalloc(&b->d_ids, sizeof(int) * (size_t)n)); b->ids_cap = n; }
+  CK(cudaMemcpyAsync(b->d_ids, env_ids, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return launch_reset(b, b->d_ids, n, 0);
+}
+
+int tfode_batch_set_actions(TfodeBatch* b, const float* actions_dev) {
+  if (!b || !actions_dev) return TFODE_EINVAL;
+  const int n = b->cfg.n_envs;
+  const float bmax = b->cfg.controller == TFODE_CTRL_CRAWLER ? b->cfg.crawler_amp : 25.0f;
+  set_actions_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, actions_dev, bmax);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_set_speed(TfodeBatch* b, const float* speed_dev) {
+  if (!b) return TFODE_EINVAL;
+  if (!speed_dev) { b->P.ext_speed = nullptr; return TFODE_OK; }
+  CK(cudaMemcpyAsync(b->ext_speed, speed_dev, sizeof(float) * (size_t)b->cfg.n_envs, cudaMemcpyDeviceToDevice, b->stream));
+  b->P.ext_speed = b->ext_speed;
+  return TFODE_OK;
+}
+
+int tfode_batch_load_policy(TfodeBatch* b, const float* w, size_t n_floats) {
+  if (!b || !w) return TFODE_EINVAL;
+  const size_t H = TFODE_MLP_HIDDEN, need = 17 * H + H + H * H + H + H * 2 + 2;
+  if (n_floats != need) { b->err = "policy blob must hold 272898 floats (W1 b1 W2 b2 W3 b3)"; return TFODE_EINVAL; }
+  if (!b->weights) CK(cudaMalloc(&b->weights, sizeof(float) * need));
+  CK(cudaMemcpyAsync(b->weights, w, sizeof(float) * need, cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  int rc = policy_tc_upload(b->tc, w, b->stream);
+  if (rc != 0) { b->err = "policy_tc_upload failed"; return TFODE_ECUDA; }
+  b->has_policy = true;
+  return TFODE_OK;
+}
+
+static int run_policy(TfodeBatch* b, const float* in, const int* list, const int* n_list, int m_direct, int max_rows, float* act_direct) {
+  const size_t H = TFODE_MLP_HIDDEN;
+  const float* W1 = b->weights; const float* b1 = W1 + 17 * H; const float* W2 = b1 + H; const float* b2 = W2 + H * H; const float* W3 = b2 + H; const float* b3 = W3 + H * 2;
+  if (b->cfg.policy_precision == TFODE_POLICY_TC) {
+    int rc = policy_tc_launch(b->tc, in, list, n_list, m_direct, max_rows, b1, b2, W3, b3, b->rec, act_direct, b->stream);
+    b->launches += 1;
+    if (rc != 0) { b->err = std::string("policy_tc_launch: ") + cudaGetErrorString(cudaGetLastError()); return TFODE_ECUDA; }
+    return TFODE_OK;
+  }
+  const int blocks = (max_rows + POL_ROWS - 1) / POL_ROWS;
+  policy_fp32_kernel<<<blocks, 256, 0, b->stream>>>(in, list, n_list, m_direct, W1, b1, W2, b2, W3, b3, b->rec, act_direct);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_step(TfodeBatch* b, int n_substeps) {
+  if (!b || n_substeps < 0) return TFODE_EINVAL;
+  if (n_substeps == 0) return TFODE_OK;
+  const int n = b->cfg.n_envs;
+  const bool mlp = b->cfg.controller == TFODE_CTRL_MLP;
+  if (mlp && !b->has_policy) { b->err = "TFODE_CTRL_MLP needs tfode_batch_load_policy first"; return TFODE_ESTATE; }
+  int rounds = 1;
+  if (mlp) {
+    int period_steps = b->cfg.ic_period > 0 ? (int)std::floor(b->cfg.ic_period / b->cfg.dt) : 1;
+    if (period_steps < 1) period_steps = 1;
+    rounds = n_substeps / period_steps + 2;
+  }
+  for (int r = 0; r < rounds; r++) {
+    StepParams P = b->P;
+    P.set_budget = (r == 0) ? n_substeps : -1;
+    step_kernel<<<launch_blocks(n), WARPS_PER_CTA * 32, b->smem_bytes, b->stream>>>(P);
+    b->launches++;
+    CK(cudaGetLastError());
+    if (mlp) {
+      int rc = run_policy(b, b->policy_in, b->parked_list, b->n_parked, 0, n, nullptr);
+      if (rc != TFODE_OK) return rc;
+      zero_int_kernel<<<1, 1, 0, b->stream>>>(b->n_parked);
+      b->launches++;
+    }
+  }
+  return TFODE_OK;
+}
+
+int tfode_policy_infer(TfodeBatch* b, const float* obs_scaled_dev, int m, float* act_dev) {
+  if (!b || !obs_scaled_dev || !act_dev || m < 0) return TFODE_EINVAL;
+  if (!b->has_policy) { b->err = "no policy loaded"; return TFODE_ESTATE; }
+  if (m == 0) return TFODE_OK;
+  return run_policy(b, obs_scaled_dev, nullptr, nullptr, m, m, act_dev);
+}
+
+int tfode_batch_observe(TfodeBatch* b, float* obs17, float* reward, uint8_t* done, int32_t* contact_count) {
+  if (!b) return TFODE_EINVAL;
+  const int n = b->cfg.n_envs;
+  observe_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, obs17, reward, done, contact_count);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_get_bodies(TfodeBatch* b, float* out_dev) {
+  if (!b || !out_dev) return TFODE_EINVAL;
+  const int n = b->cfg.n_envs * NB;
+  bodies_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, b->cfg.n_envs, out_dev);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, int* n_rows_host) {
+  if (!b || !n_rows_host) return TFODE_EINVAL;
+  int cnt = 0;
+  CK(cudaMemcpyAsync(&cnt, b->n_trans, sizeof(int), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  int avail = cnt < b->trans_cap ? cnt : b->trans_cap;
+  int take = avail < max_rows ? avail : max_rows;
+  if (out_dev && take > 0) CK(cudaMemcpyAsync(out_dev, b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)take, cudaMemcpyDeviceToDevice, b->stream));
+  CK(cudaMemsetAsync(b->n_trans, 0, sizeof(int), b->stream));
+  *n_rows_host = cnt;  // rows produced (rows beyond the ring capacity were dropped)
+  return TFODE_OK;
+}
+
+int tfode_batch_rollout_host(TfodeBatch* b, const float* actions_host, int n_substeps, float* obs17_host, float* reward_host, uint8_t* done_host) {
+  if (!b) return TFODE_EINVAL;
+  const int n = b->cfg.n_envs;
+  float* pin_act = b->h_pin; float* pin_obs = pin_act + 2 * (size_t)n; float* pin_rew = pin_obs + 17 * (size_t)n; uint8_t* pin_done = (uint8_t*)(pin_rew + n);
+  if (actions_host) {
+    std::memcpy(pin_act, actions_host, sizeof(float) * 2 * (size_t)n);
+    CK(cudaMemcpyAsync(b->d_act, pin_act, sizeof(float) * 2 * (size_t)n, cudaMemcpyHostToDevice, b->stream));
+    int rc = tfode_batch_set_actions(b, b->d_act); if (rc) return rc;
+  }
+  int rc = tfode_batch_step(b, n_substeps); if (rc) return rc;
+  rc = tfode_batch_observe(b, obs17_host ? b->d_obs : nullptr, reward_host ? b->d_rew : nullptr, done_host ? b->d_done : nullptr, nullptr); if (rc) return rc;
+  if (obs17_host) CK(cudaMemcpyAsync(pin_obs, b->d_obs, sizeof(float) * 17 * (size_t)n, cudaMemcpyDeviceToHost, b->stream));
+  if (reward_host) CK(cudaMemcpyAsync(pin_rew, b->d_rew, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, b->stream));
+  if (done_host) CK(cudaMemcpyAsync(pin_done, b->d_done, (size_t)n, cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  if (obs17_host) std::memcpy(obs17_host, pin_obs, sizeof(float) * 17 * (size_t)n);
+  if (reward_host) std::memcpy(reward_host, pin_rew, sizeof(float) * (size_t)n);
+  if (done_host) std::memcpy(done_host, pin_done, (size_t)n);
+  return TFODE_OK;
+}
+
+int tfode_batch_get_state(TfodeBatch* b, int env, TfodeEnvState* s) {
+  if (!b || !s || env < 0 || env >= b->cfg.n_envs) return TFODE_EINVAL;
+  EnvRec r;
+  CK(cudaMemcpyAsync(&r, b->rec + env, sizeof(EnvRec), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  std::memset(s, 0, sizeof(*s));
+  const Ctrl& c = r.c;
+  for (int bd = 0; bd < NB; bd++) {
+    for (int k = 0; k < 3; k++) { s->pos[bd][k] = r.body[F_POS + k][bd]; s->lvel[bd][k] = r.body[F_LVEL + k][bd]; s->avel[bd][k] = r.body[F_AVEL + k][bd]; s->facc[bd][k] = r.body[F_FACC + k][bd]; s->tacc[bd][k] = r.body[F_TACC + k][bd]; }
+    for (int k = 0; k < 4; k++) s->quat[bd][k] = r.body[F_QUAT + k][bd];
+  }
+  if (b->cfg.scene != TFODE_SCENE_STEP_BOXES) for (int bd = NBR; bd < NB; bd++) { for (int k = 0; k < 3; k++) s->pos[bd][k] = 0; s->quat[bd][0] = 1; s->quat[bd][1] = s->quat[bd][2] = s->quat[bd][3] = 0; }
+  for (int i = 0; i < 4; i++) { s->wheel_vel[i] = c.wheel_vel[i]; s->wheel_fmax[i] = c.wheel_fmax[i]; s->W[i] = c.W[i]; }
+  s->servo_vel = c.servo_vel; s->robot_speed = c.robot_speed; s->steering_rate = c.steering_rate; s->boggie_torque = c.boggie_torque;
+  s->ic_clock = c.ic_clock; s->ic_period = c.ic_period;
+  for (int i = 0; i < 12; i++) { for (int k = 0; k < 4; k++) s->filt[i][k] = c.filt[i][k]; s->ft[i] = c.ft[i]; }
+  for (int k = 0; k < 3; k++) s->last_pos[k] = c.last_pos[k];
+  s->total_reward = c.total_reward; s->last_reward = c.last_reward;
+  for (int i = 0; i < 17; i++) s->last_state[i] = c.last_state[i];
+  s->step_yaw_deg = c.step_yaw_deg; s->crawler_amp = c.cr_amp; s->crawler_rate = c.cr_rate; s->crawler_dtorque_dt = c.cr_dtorque_dt;
+  s->speed = c.speed; s->ic_start = c.ic_start; s->time_steps = c.time_steps; s->lcg_seed = c.lcg_seed; s->episode = c.episode; s->tick = c.tick;
+  s->ic_activated = c.ic_activated; s->ic_tick = c.ic_tick; s->servo_mode_vel = c.servo_mode_vel; s->has_last_state = c.has_last_state;
+  s->explore = c.explore; s->fork_collision = c.fork_collision; s->crawler_phase = c.cr_phase; s->done = c.done_call; s->term_reason = c.term_reason;
+  s->n_contacts = c.n_contacts; s->episodes_done = c.episodes_done;
+  return TFODE_OK;
+}
+
+int tfode_batch_set_state(TfodeBatch* b, int env, const TfodeEnvState* s) {
+  if (!b || !s || env < 0 || env >= b->cfg.n_envs) return TFODE_EINVAL;
+  EnvRec r;
+  CK(cudaMemcpyAsync(&r, b->rec + env, sizeof(EnvRec), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  if (s->episode != r.c.episode) { b->err = "set_state: episode mismatch (per-episode scene constants differ)"; return TFODE_EINVAL; }
+  Ctrl& c = r.c;
+  const int nb = b->cfg.scene == TFODE_SCENE_STEP_BOXES ? NB : NBR;
+  for (int bd = 0; bd < nb; bd++) {
+    for (int k = 0; k < 3; k++) { r.body[F_POS + k][bd] = (float)s->pos[bd][k]; r.body[F_LVEL + k][bd] = (float)s->lvel[bd][k]; r.body[F_AVEL + k][bd] = (float)s->avel[bd][k]; r.body[F_FACC + k][bd] = (float)s->facc[bd][k]; r.body[F_TACC + k][bd] = (float)s->tacc[bd][k]; }
+    for (int k = 0; k < 4; k++) r.body[F_QUAT + k][bd] = (float)s->quat[bd][k];
+  }
+  for (int i = 0; i < 4; i++) { c.wheel_vel[i] = (float)s->wheel_vel[i]; c.wheel_fmax[i] = (float)s->wheel_fmax[i]; c.W[i] = (float)s->W[i]; }
+  c.servo_vel = (float)s->servo_vel; c.robot_speed = s->robot_speed; c.steering_rate = s->steering_rate; c.boggie_torque = s->boggie_torque;
+  c.ic_clock = s->ic_clock; c.ic_period = (float)s->ic_period;
+  for (int i = 0; i < 12; i++) { for (int k = 0; k < 4; k++) c.filt[i][k] = s->filt[i][k]; c.ft[i] = (float)s->ft[i]; }
+  for (int k = 0; k < 3; k++) c.last_pos[k] = s->last_pos[k];
+  c.total_reward = s->total_reward; c.last_reward = s->last_reward;
+  for (int i = 0; i < 17; i++) c.last_state[i] = (float)s->last_state[i];
+  c.speed = s->speed; c.ic_start = s->ic_start; c.time_steps = s->time_steps; c.lcg_seed = s->lcg_seed; c.tick = s->tick;
+  c.ic_activated = s->ic_activated; c.ic_tick = s->ic_tick; c.servo_mode_vel = s->servo_mode_vel; c.has_last_state = s->has_last_state;
+  c.explore = s->explore; c.fork_collision = s->fork_collision; c.cr_phase = s->crawler_phase; c.done_call = s->done; c.term_reason = s->term_reason;
+  c.n_contacts = s->n_contacts; c.episodes_done = s->episodes_done; c.parked = 0; c.frozen = 0;
+  CK(cudaMemcpyAsync(b->rec + env, &r, sizeof(EnvRec), cudaMemcpyHostToDevice, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  return TFODE_OK;
+}
+
+}  // extern "C"

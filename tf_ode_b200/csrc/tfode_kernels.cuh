@@ -1,0 +1,981 @@
+// step_kernel and the small per-env utility kernels.  See tfode_step.cuh for the design.
+#pragma once
+#include "tfode_step.cuh"
+
+namespace tfode {
+
+constexpr int WARPS_PER_CTA = 4;
+
+// warp-inclusive scan of small counts
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { int t = __shfl_up_sync(FULLMASK, v, d); if (lane >= d) v += t; }
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// (re)construction of an environment: everything simulation() builds (src/rover_training_1.cc:41-125)
+// body registers of lane b are returned through the references; ctrl block is written by lane 0.
+// ------------------------------------------------------------------------------------------------
+__device__ void reset_env(WarpSm& S, const StepParams& P, uint32_t env_global, uint32_t episode, int lane,
+                          float* pos, float* q, float* lvel, float* avel, float* facc, float* tacc) {
+  const Model& M = g_model;
+  const TfodeBatchConfig& cfg = P.cfg;
+  if (lane == 0) {
+    Ctrl& c = S.c;
+    const int keep_explore = c.explore, keep_eps = c.episodes_done, keep_done = c.done_call, keep_term = c.term_reason;
+    const float ler = c.last_ep_return, lex = c.last_ep_x, ley = c.last_ep_y; const int les = c.last_ep_steps;
+    uint32_t rnd[4]; philox(cfg.seed, env_global, episode, 0, 0, rnd);
+    double yaw = (double)cfg.step_yaw_deg + (double)cfg.step_yaw_jitter_deg * (double)u11(rnd[0]);
+    float ic_start = (float)((double)cfg.ic_start + (double)cfg.ic_start_jitter * (double)u11(rnd[1]));
+    float amp = (float)((double)cfg.crawler_amp + (double)cfg.crawler_amp_jitter * (double)u11(rnd[2]));
+    float rate = (float)((double)cfg.crawler_rate + (double)cfg.crawler_rate_jitter * (double)u11(rnd[3]));
+    unsigned char* z = reinterpret_cast<unsigned char*>(&c);
+    for (int i = 0; i < (int)sizeof(Ctrl); i++) z[i] = 0;
+    c.explore = keep_explore; c.episodes_done = keep_eps; c.done_call = keep_done; c.term_reason = keep_term;
+    c.last_ep_return = ler; c.last_ep_x = lex; c.last_ep_y = ley; c.last_ep_steps = les;
+    c.episode = episode; c.ic_start = ic_start; c.step_yaw_deg = (float)yaw; c.cr_amp = amp; c.cr_rate = rate;
+    c.ic_period = cfg.ic_period; c.ic_activated = cfg.ic_initially_active != 0;
+    for (int i = 0; i < 4; i++) c.wheel_fmax[i] = 25.4f;  // WHEELS_MAX_TORQUE, src/rover_1.cc:229
+    c.cr_phase = 1;
+    c.cr_dtorque_dt = (double)(2 * amp / cfg.crawler_dt_torque);
+    // step box 0: dRFromEulerAngles(0,0,yaw) -> quaternion (ode/object.cc:116-121); fix joint frames (object.cc:155-179)
+    double psi = yaw * 3.14159265358979323846 / 180.0;
+    double cp = cos(psi), sp = sin(psi);
+    double tr = 2 * cp + 1;  // |yaw| < 120 deg
+    double s = sqrt(tr + 1), q0 = 0.5 * s, q3 = (-sp - sp) * (0.5 / s);
+    double nrm = 1.0 / sqrt(q0 * q0 + q3 * q3); q0 *= nrm; q3 *= nrm;
+    S.aux[0] = (float)q0; S.aux[1] = (float)q3;
+    c.fix_qrel[0][0] = (float)q0; c.fix_qrel[0][1] = 0; c.fix_qrel[0][2] = 0; c.fix_qrel[0][3] = (float)(-q3);
+    c.fix_qrel[1][0] = 1; c.fix_qrel[1][1] = 0; c.fix_qrel[1][2] = 0; c.fix_qrel[1][3] = 0;
+    for (int k = 0; k < 3; k++) { c.fix_offset[0][k] = M.pos0[10][k]; c.fix_offset[1][k] = M.pos0[11][k]; }
+    // Rover_1_tf ctor: _last_pos = GetPosition() at the construction pose (identity rotation of the main body)
+    for (int k = 0; k < 3; k++) c.last_pos[k] = (double)(M.pos0[0][k] + M.getpos_rel[k]);
+  }
+  __syncwarp();
+  if (lane < NB) {
+    for (int k = 0; k < 3; k++) { pos[k] = M.pos0[lane][k]; lvel[k] = 0; avel[k] = 0; facc[k] = 0; tacc[k] = 0; }
+    for (int k = 0; k < 4; k++) q[k] = M.quat0[lane][k];
+    if (lane == 10) { q[0] = S.aux[0]; q[1] = 0; q[2] = 0; q[3] = S.aux[1]; }
+  }
+  __syncwarp();
+}
+
+// lane b publishes its pose/velocity to the shared body table
+__device__ __forceinline__ void publish_body(WarpSm& S, int lane, const float* pos, const float* q, const float* R, const float* lvel, const float* avel) {
+  if (lane < NB) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) { S.bpos[lane][k] = pos[k]; S.bvel[lane][k] = lvel[k]; S.bvel[lane][3 + k] = avel[k]; }
+#pragma unroll
+    for (int k = 0; k < 4; k++) S.bq[lane][k] = q[k];
+#pragma unroll
+    for (int k = 0; k < 9; k++) S.bR[lane][k] = R[k];
+  }
+}
+
+// joint kinematic read-outs of the current pose (servo angle/rate, boggie angle, wheel rates)
+__device__ __forceinline__ void joint_readouts(WarpSm& S, int lane) {
+  if (lane >= 1 && lane <= 6) {
+    if (lane <= 2) S.c.jq_angle[lane] = hinge_angle(S, lane);
+    S.c.jq_rate[lane] = hinge_rate(S, lane);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__device__ void append_transition(const StepParams& P, const Ctrl& c, uint32_t env_global, bool terminal, float penalty) {
+  int slot = atomicAdd(P.n_trans, 1);
+  if (slot >= P.trans_cap) return;
+  float* row = P.trans + (size_t)slot * TFODE_TRANSITION_WIDTH;
+  row[0] = (float)env_global;
+  for (int i = 0; i < 17; i++) row[1 + i] = c.pending[i];
+  row[18] = c.pending[17]; row[19] = c.pending[18];
+  row[20] = c.pending[19] - penalty; row[21] = terminal ? 1.0f : 0.0f;
+  for (int i = 0; i < 17; i++) row[22 + i] = c.pending[20 + i];
+  for (int i = 39; i < TFODE_TRANSITION_WIDTH; i++) row[i] = 0;
+}
+
+// Rover_1_tf::GetState (src/rover_1_tf.cc:60-77) from the shared body table; lane-0 code
+__device__ void get_state17(const WarpSm& S, float* s) {
+  const float* R = S.bR[0];
+  float vx0 = R[0], vx1 = R[3], vx2 = R[6];  // body x axis in the world
+  float direction = asinf(vx1) * 57.29577951308232f;
+  if (vx0 < 0) direction = (vx1 > 0 ? 1.0f : -1.0f) * 180.0f - direction;
+  s[0] = direction;
+  s[1] = S.c.jq_angle[1] * 57.29577951308232f;
+  s[2] = asinf(R[7]) * 57.29577951308232f;   // body y axis, z component
+  s[3] = asinf(-vx2) * 57.29577951308232f;
+  s[4] = S.c.jq_angle[2] * 57.29577951308232f;
+  for (int i = 0; i < 12; i++) s[5 + i] = S.c.ft[i];
+}
+
+// ================================================================================================
+//                                         THE STEP KERNEL
+// ================================================================================================
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int env = blockIdx.x * WARPS_PER_CTA + wid;
+  if (env >= P.n_envs) return;
+  WarpSm& S = reinterpret_cast<WarpSm*>(smem_raw)[wid];
+  const Model& M = g_model;
+  const TfodeBatchConfig& cfg = P.cfg;
+  const uint32_t env_global = (uint32_t)(cfg.env_id_offset + env);
+
+  int budget = (P.set_budget >= 0) ? P.set_budget : P.budget[env];
+  if (budget <= 0 && P.set_budget < 0) return;
+
+  // ---------------------------------------------------------------- load the record (coalesced float4 -> smem staging -> registers)
+  EnvRec* grec = P.rec + env;
+  {
+    const float4* src = reinterpret_cast<const float4*>(grec);
+    float4* dst = reinterpret_cast<float4*>(&S.rowJ[0][0]);
+    constexpr int N4 = sizeof(EnvRec) / 16;
+    for (int i = lane; i < N4; i += 32) dst[i] = src[i];
+  }
+  __syncwarp();
+  float pos[3], q[4], R[9], lvel[3], avel[3], facc[3], tacc[3];
+  {
+    const EnvRec* st = reinterpret_cast<const EnvRec*>(&S.rowJ[0][0]);
+    const int b = lane < NB ? lane : 0;
+#pragma unroll
+    for (int k = 0; k < 3; k++) { pos[k] = st->body[F_POS + k][b]; lvel[k] = st->body[F_LVEL + k][b]; avel[k] = st->body[F_AVEL + k][b]; facc[k] = st->body[F_FACC + k][b]; tacc[k] = st->body[F_TACC + k][b]; }
+#pragma unroll
+    for (int k = 0; k < 4; k++) q[k] = st->body[F_QUAT + k][b];
+    const uint32_t* cs = reinterpret_cast<const uint32_t*>(&st->c);
+    uint32_t* cd = reinterpret_cast<uint32_t*>(&S.c);
+    for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
+  }
+  __syncwarp();
+  if (P.set_budget >= 0 && lane == 0) S.c.done_call = 0;
+  quatToR(R, q);
+  publish_body(S, lane, pos, q, R, lvel, avel);
+  __syncwarp();
+  joint_readouts(S, lane);  // derived from the pose: recomputed so that records written by set_state are consistent
+  __syncwarp();
+
+  const int nb_active = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? NB : NBR;
+  const int nj_active = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? NJ : NJ - 2;
+  const bool body_lane = lane < nb_active;
+  const float h = cfg.dt;
+  const float fps = 1.0f / h;
+  const float invMass = body_lane ? M.invMass[lane] : 0.0f;
+  const float ext_speed = P.ext_speed ? P.ext_speed[env] : 0.0f;
+  const int maxc = min(cfg.max_contacts, MAXC);
+
+  // ================================================================== sub-step loop
+  while (budget > 0) {
+    if (S.c.frozen) { budget = 0; break; }
+    bool do_part_a = S.c.parked == 0;
+    if (S.c.parked == 1) break;  // still waiting for the policy kernel (should not happen inside a call)
+
+    if (do_part_a) {
+      // ------------------------------------------------------------ scene lambda prologue (rover_training_1.cc:129-136)
+      if (lane == 0) {
+        Ctrl& c = S.c;
+        c.done_step = 0;
+        if (P.ext_speed) c.robot_speed = fmin(fmax(-(double)M.robot_max_speed, (double)ext_speed), (double)M.robot_max_speed);
+        else if (cfg.term > 0 && fabsf(c.speed) <= fabsf(cfg.speedf)) {
+          c.speed += cfg.speedf / cfg.term * cfg.dt;
+          c.robot_speed = fmin(fmax(-(double)M.robot_max_speed, (double)c.speed), (double)M.robot_max_speed);
+        }
+        float timef = (float)c.time_steps * cfg.dt;
+        if (!c.ic_activated && cfg.ic_start >= 0 && (double)timef >= (double)c.ic_start) c.ic_activated = 1;
+      }
+
+      // ------------------------------------------------------------ collide (ode/environment.cc:56-150)
+      int nc_total = 0;    // generated contacts (uniform)
+      unsigned fork_hit = 0;
+      const int n_terrain = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? 3 : (cfg.scene == TFODE_SCENE_HEIGHTFIELD ? 2 : 1);
+      for (int t = 0; t < n_terrain; t++) {
+        const int tkind = (t == 0) ? T_PLANE : (cfg.scene == TFODE_SCENE_STEP_BOXES ? T_BOX : T_HF);
+        const int tbody = (tkind == T_BOX) ? NBR + (t - 1) : 15;
+        const float* tpos = (tkind == T_BOX) ? S.bpos[tbody] : S.bpos[0];
+        const float* tR = (tkind == T_BOX) ? S.bR[tbody] : S.bR[0];
+        const float* tside = M.step_side[(tkind == T_BOX) ? (t - 1) : 0];
+        for (int pass = 0; pass < 8; pass++) {
+          CG cg[4]; int n = 0; int gbody = 0; int soft = 0;
+          if (pass == 0) {
+            if (lane < NNS) {
+              const int g = lane;
+              gbody = M.ns_body[g];
+              float gp[3], gR[9];
+              const float* bR = S.bR[gbody];
+              mulRv(gp, bR, M.ns_off[g]);
+              gp[0] += S.bpos[gbody][0]; gp[1] += S.bpos[gbody][1]; gp[2] += S.bpos[gbody][2];
+              if (M.ns_rot[g]) {  // R * [[1,0,0],[0,0,1],[0,-1,0]] : columns (c0, -c2, c1)
+#pragma unroll
+                for (int r = 0; r < 3; r++) { gR[r * 3 + 0] = bR[r * 3 + 0]; gR[r * 3 + 1] = -bR[r * 3 + 2]; gR[r * 3 + 2] = bR[r * 3 + 1]; }
+              } else {
+#pragma unroll
+                for (int k = 0; k < 9; k++) gR[k] = bR[k];
+              }
+              const float* dim = M.ns_dim[g];
+              if (M.ns_type[g] == 2) {
+                if (tkind == T_PLANE) n = col_cyl_plane(gp, gR, dim[0], dim[1], cg);
+                else n = col_cyl_samples(tkind, gp, gR, dim[0], dim[1], tpos, tR, tside, P.hf, cg);
+                if (M.ns_cb[g] && cfg.fork_callback) {  // near-callback AABB test (Q10)
+                  float lo[3], hi[3];
+#pragma unroll
+                  for (int k = 0; k < 3; k++) {
+                    float rr = gR[k * 3 + 2];
+                    float range = fabsf(rr * dim[1] * 0.5f) + dim[0] * sqrtf(fmaxf(0.0f, 1.0f - rr * rr));
+                    lo[k] = gp[k] - range; hi[k] = gp[k] + range;
+                  }
+                  bool ov;
+                  if (tkind == T_PLANE) ov = lo[2] <= 0.0f;
+                  else if (tkind == T_BOX) {
+                    ov = true;
+#pragma unroll
+                    for (int k = 0; k < 3; k++) {
+                      float range = 0.5f * (fabsf(tR[k * 3 + 0] * tside[0]) + fabsf(tR[k * 3 + 1] * tside[1]) + fabsf(tR[k * 3 + 2] * tside[2]));
+                      if (lo[k] > tpos[k] + range || hi[k] < tpos[k] - range) ov = false;
+                    }
+                  } else {
+                    ov = !(lo[0] > P.hf.pos[0] + P.hf.length * 0.5f || hi[0] < P.hf.pos[0] - P.hf.length * 0.5f ||
+                           lo[1] > P.hf.pos[1] + P.hf.width * 0.5f || hi[1] < P.hf.pos[1] - P.hf.width * 0.5f ||
+                           lo[2] > P.hf.pos[2] + 1.0f || hi[2] < P.hf.pos[2] - 1.0f);
+                  }
+                  if (ov) fork_hit = 1;
+                }
+              } else {
+                if (tkind == T_PLANE) n = col_box_plane(gp, gR, dim, cg);
+                else n = col_box_samples(tkind, gp, gR, dim, tpos, tR, tside, P.hf, cg);
+              }
+            }
+          } else {
+            const int s = (pass - 1) * 32 + lane;
+            if (s < NSPHERE) {
+              const int w = s / 50, k = s - w * 50;
+              gbody = 6 + w; soft = (k == 49);
+              const float* bR = S.bR[gbody];
+              const float rx = M.ring[k][0], ry = M.ring[k][1];
+              float c[3] = {S.bpos[gbody][0] + bR[0] * rx + bR[1] * ry, S.bpos[gbody][1] + bR[3] * rx + bR[4] * ry, S.bpos[gbody][2] + bR[6] * rx + bR[7] * ry};
+              if (tkind == T_PLANE) n = col_sphere_plane(c, M.sphere_r, cg);
+              else if (tkind == T_BOX) n = col_sphere_box(c, M.sphere_r, tpos, tR, tside, cg);
+              else n = col_sphere_hf(P.hf, c, M.sphere_r, cg);
+            }
+          }
+          if (__any_sync(FULLMASK, n > 0)) {
+            int incl = warp_incl_scan(n, lane);
+            int base = nc_total + incl - n;
+            for (int i = 0; i < n; i++) {
+              int slot = base + i;
+              if (slot < maxc) {
+                float* d = S.cont[slot];
+                d[0] = cg[i].p[0]; d[1] = cg[i].p[1]; d[2] = cg[i].p[2]; d[3] = cg[i].n[0]; d[4] = cg[i].n[1]; d[5] = cg[i].n[2]; d[6] = cg[i].depth;
+                d[7] = __int_as_float(gbody | (tbody << 4) | (soft << 8));
+              }
+            }
+            nc_total += __shfl_sync(FULLMASK, incl, 31);
+          }
+        }
+      }
+      if (__any_sync(FULLMASK, fork_hit != 0) && lane == 0) S.c.fork_collision = 1;
+      const int nc = min(nc_total, maxc);
+      if (lane == 0) S.c.n_contacts = nc_total;
+      __syncwarp();
+
+      // ------------------------------------------------------------ islands: which rover groups touch which step box
+      int lab_of_group[NISL];
+      {
+        unsigned adj3 = 0, adj4 = 0;
+        if (lane < nc) {
+          int info = __float_as_int(S.cont[lane][7]);
+          int b1 = info & 15, b2 = (info >> 4) & 15;
+          if (b2 == 10) adj3 = 1u << body_group(b1);
+          if (b2 == 11) adj4 = 1u << body_group(b1);
+        }
+        adj3 = __reduce_or_sync(FULLMASK, adj3); adj4 = __reduce_or_sync(FULLMASK, adj4);
+        unsigned S3 = (1u << 3) | adj3, S4 = (1u << 4) | adj4;
+        if (S3 & S4) { S3 |= S4; S4 = S3; }
+#pragma unroll
+        for (int g = 0; g < NISL; g++) lab_of_group[g] = (S3 >> g & 1u) ? (__ffs(S3) - 1) : ((S4 >> g & 1u) ? (__ffs(S4) - 1) : g);
+      }
+
+      // ------------------------------------------------------------ per-body prep: world inverse inertia, gyroscopic torque, gravity, v/h + invM f
+      float iI[6] = {0, 0, 0, 0, 0, 0};  // xx xy xz yy yz zz
+      if (body_lane) {
+        const float i0 = M.invIb[lane][0], i1 = M.invIb[lane][1], i2 = M.invIb[lane][2];
+        iI[0] = R[0] * (i0 * R[0]) + R[1] * (i1 * R[1]) + R[2] * (i2 * R[2]);
+        iI[1] = R[0] * (i0 * R[3]) + R[1] * (i1 * R[4]) + R[2] * (i2 * R[5]);
+        iI[2] = R[0] * (i0 * R[6]) + R[1] * (i1 * R[7]) + R[2] * (i2 * R[8]);
+        iI[3] = R[3] * (i0 * R[3]) + R[4] * (i1 * R[4]) + R[5] * (i2 * R[5]);
+        iI[4] = R[3] * (i0 * R[6]) + R[4] * (i1 * R[7]) + R[5] * (i2 * R[8]);
+        iI[5] = R[6] * (i0 * R[6]) + R[7] * (i1 * R[7]) + R[8] * (i2 * R[8]);
+        // gyroscopic: tacc -= w x (I w), I w = R diag(Ib) R^T w
+        float wl[3] = {R[0] * avel[0] + R[3] * avel[1] + R[6] * avel[2], R[1] * avel[0] + R[4] * avel[1] + R[7] * avel[2], R[2] * avel[0] + R[5] * avel[1] + R[8] * avel[2]};
+        wl[0] *= M.Ib[lane][0]; wl[1] *= M.Ib[lane][1]; wl[2] *= M.Ib[lane][2];
+        float Iw[3]; mulRv(Iw, R, wl);
+        float cr[3]; cross3(cr, avel, Iw);
+        tacc[0] -= cr[0]; tacc[1] -= cr[1]; tacc[2] -= cr[2];
+        facc[2] += M.mass[lane] * -9.80665f;
+        float* bt = S.btmp[lane];
+        bt[0] = facc[0] * invMass + lvel[0] * fps; bt[1] = facc[1] * invMass + lvel[1] * fps; bt[2] = facc[2] * invMass + lvel[2] * fps;
+        bt[3] = iI[0] * tacc[0] + iI[1] * tacc[1] + iI[2] * tacc[2] + avel[0] * fps;
+        bt[4] = iI[1] * tacc[0] + iI[3] * tacc[1] + iI[4] * tacc[2] + avel[1] * fps;
+        bt[5] = iI[2] * tacc[0] + iI[4] * tacc[1] + iI[5] * tacc[2] + avel[2] * fps;
+        float* bi = S.binvI[lane];
+#pragma unroll
+        for (int k = 0; k < 6; k++) bi[k] = iI[k];
+        bi[6] = invMass;
+      }
+
+      // ------------------------------------------------------------ joint rows (lane j = joint j)
+      int jm = 0;        // rows of my joint
+      int jlimit = 0; float jlimit_err = 0;
+      float jfmax = 0, jvel = 0;
+      if (lane < nj_active) {
+        const int j = lane;
+        if (!M.jslider[j]) {
+          if (j == 1) { jfmax = 180.0f; jvel = S.c.servo_vel; }      // STEERING_MAX_TORQUE
+          else if (j >= 3) { jfmax = S.c.wheel_fmax[j - 3]; jvel = S.c.wheel_vel[j - 3]; }
+          jm = jfmax > 0 ? 6 : 5;
+          if ((M.lostop[j] >= -3.14159265358979323846f || M.histop[j] <= 3.14159265358979323846f) && M.lostop[j] <= M.histop[j]) {
+            float ang = S.c.jq_angle[j];
+            if (ang <= M.lostop[j]) { jlimit = 1; jlimit_err = ang - M.lostop[j]; jm = 6; }
+            else if (ang >= M.histop[j]) { jlimit = 2; jlimit_err = ang - M.histop[j]; jm = 6; }
+          }
+        } else jm = 6;  // lo = hi = 0: the limit row is always present
+      }
+      int jincl = warp_incl_scan(jm, lane);
+      const int jrow0 = jincl - jm;
+      const int njrows = __shfl_sync(FULLMASK, jincl, 31);
+      const int m_total = njrows + 3 * nc;
+      if (lane < nj_active) {
+        const int j = lane;
+        const int b1 = M.jb1[j], b2 = M.jb2[j];  // b2 = 15 : world
+        const bool has2 = b2 < NB;
+        const float* R1 = S.bR[b1]; const float* x1 = S.bpos[b1];
+        const float* R2 = S.bR[has2 ? b2 : b1]; const float* x2 = S.bpos[has2 ? b2 : b1];
+        const float k_erp = fps * cfg.erp;
+        const int hdr = b1 | (b2 << 4) | (255 << 8);
+        for (int r = 0; r < jm; r++) {
+          float* Jr = S.rowJ[jrow0 + r];
+#pragma unroll
+          for (int k = 0; k < 12; k++) Jr[k] = 0.0f;
+          float* Sr = S.rowS[jrow0 + r];
+          Sr[RS_C] = 0.0f; Sr[RS_ADCFM] = cfg.cfm; Sr[RS_LO] = -CUDART_INF_F; Sr[RS_HI] = CUDART_INF_F; Sr[RS_LAM] = 0.0f;
+          Sr[RS_HDR] = __int_as_float(hdr);
+        }
+        if (!M.jslider[j]) {
+          // ball part (setBall)
+          float a1[3], a2[3];
+          mulRv(a1, R1, M.anchor1[j]); mulRv(a2, R2, M.anchor2[j]);
+          for (int r = 0; r < 3; r++) {
+            float* Jr = S.rowJ[jrow0 + r];
+            Jr[r] = 1.0f; Jr[6 + r] = -1.0f;
+            S.rowS[jrow0 + r][RS_C] = k_erp * (a2[r] + x2[r] - a1[r] - x1[r]);
+          }
+          { float* J0 = S.rowJ[jrow0 + 0]; float* J1 = S.rowJ[jrow0 + 1]; float* J2 = S.rowJ[jrow0 + 2];
+            J0[4] = a1[2]; J0[5] = -a1[1]; J1[3] = -a1[2]; J1[5] = a1[0]; J2[3] = a1[1]; J2[4] = -a1[0];
+            J0[10] = -a2[2]; J0[11] = a2[1]; J1[9] = a2[2]; J1[11] = -a2[0]; J2[9] = -a2[1]; J2[10] = a2[0]; }
+          float ax1[3], ax2[3], pp[3], qq[3], bb[3];
+          mulRv(ax1, R1, M.axis1[j]); mulRv(ax2, R2, M.axis2[j]);
+          planeSpace(ax1, pp, qq);
+          cross3(bb, ax1, ax2);
+          { float* J3 = S.rowJ[jrow0 + 3]; float* J4 = S.rowJ[jrow0 + 4];
+            for (int k = 0; k < 3; k++) { J3[3 + k] = pp[k]; J3[9 + k] = -pp[k]; J4[3 + k] = qq[k]; J4[9 + k] = -qq[k]; }
+            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(bb, pp); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(bb, qq); }
+          if (jm == 6) {
+            float* J5 = S.rowJ[jrow0 + 5]; float* S5 = S.rowS[jrow0 + 5];
+            for (int k = 0; k < 3; k++) { J5[3 + k] = ax1[k]; J5[9 + k] = -ax1[k]; }
+            if (jlimit) {  // unpowered joint at a stop (the boggie hinge)
+              S5[RS_C] = -k_erp * jlimit_err;
+              if (jlimit == 1) { S5[RS_LO] = 0.0f; S5[RS_HI] = CUDART_INF_F; } else { S5[RS_LO] = -CUDART_INF_F; S5[RS_HI] = 0.0f; }
+            } else { S5[RS_C] = jvel; S5[RS_LO] = -jfmax; S5[RS_HI] = jfmax; }
+          }
+        } else {
+          // slider: battery clamp (two bodies) or step fix (body - world)
+          const float* qrel = (j >= 7) ? S.c.fix_qrel[j - 7] : M.qrel[j];
+          const float* offs = (j >= 7) ? S.c.fix_offset[j - 7] : M.offset[j];
+          float qerr[4];
+          if (has2) { float t4[4]; qmul_inv_a(t4, S.bq[b1], S.bq[b2]); qmul_inv_b(qerr, t4, qrel); }
+          else qmul_inv_ab(qerr, S.bq[b1], qrel);
+          if (qerr[0] < 0) { qerr[1] = -qerr[1]; qerr[2] = -qerr[2]; qerr[3] = -qerr[3]; }
+          float e[3]; mulRv(e, R1, qerr + 1);
+          for (int r = 0; r < 3; r++) {
+            float* Jr = S.rowJ[jrow0 + r];
+            Jr[3 + r] = 1.0f; if (has2) Jr[9 + r] = -1.0f;
+            S.rowS[jrow0 + r][RS_C] = 2 * k_erp * e[r];
+          }
+          float ax1[3], pp[3], qq[3];
+          mulRv(ax1, R1, M.axis1[j]);
+          planeSpace(ax1, pp, qq);
+          float* J3 = S.rowJ[jrow0 + 3]; float* J4 = S.rowJ[jrow0 + 4]; float* J5 = S.rowJ[jrow0 + 5];
+          float cvec[3] = {0, 0, 0};
+          float posn;
+          if (has2) {
+            for (int k = 0; k < 3; k++) cvec[k] = x2[k] - x1[k];
+            float t3[3];
+            cross3(t3, cvec, pp); for (int k = 0; k < 3; k++) { J3[3 + k] = 0.5f * t3[k]; J3[9 + k] = 0.5f * t3[k]; }
+            cross3(t3, cvec, qq); for (int k = 0; k < 3; k++) { J4[3 + k] = 0.5f * t3[k]; J4[9 + k] = 0.5f * t3[k]; }
+            for (int k = 0; k < 3; k++) { J3[6 + k] = -pp[k]; J4[6 + k] = -qq[k]; }
+            float ofs[3]; mulRv(ofs, R2, offs);
+            float cc[3] = {cvec[0] + ofs[0], cvec[1] + ofs[1], cvec[2] + ofs[2]};
+            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(pp, cc); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(qq, cc);
+            float qv[3] = {x1[0] - ofs[0] - x2[0], x1[1] - ofs[1] - x2[1], x1[2] - ofs[2] - x2[2]};
+            posn = dot3(ax1, qv);
+            // limit row with linear torque decoupling
+            float cl[3] = {0.5f * cvec[0], 0.5f * cvec[1], 0.5f * cvec[2]}, ltd[3];
+            cross3(ltd, cl, ax1);
+            for (int k = 0; k < 3; k++) { J5[k] = ax1[k]; J5[6 + k] = -ax1[k]; J5[3 + k] = ltd[k]; J5[9 + k] = ltd[k]; }
+          } else {
+            float ofs[3] = {offs[0] - x1[0], offs[1] - x1[1], offs[2] - x1[2]};
+            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(pp, ofs); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(qq, ofs);
+            float qv[3] = {x1[0] - offs[0], x1[1] - offs[1], x1[2] - offs[2]};
+            posn = dot3(ax1, qv);
+            for (int k = 0; k < 3; k++) J5[k] = ax1[k];
+          }
+          for (int k = 0; k < 3; k++) { J3[k] = pp[k]; J4[k] = qq[k]; }
+          S.rowS[jrow0 + 5][RS_C] = -k_erp * posn;  // lo = hi = 0: equality, unbounded
+        }
+      }
+      // ------------------------------------------------------------ contact rows (lane c = contact c), dxJointContact::getInfo2
+      if (lane < nc) {
+        const float* cd = S.cont[lane];
+        const int info = __float_as_int(cd[7]);
+        const int b1 = info & 15, b2 = (info >> 4) & 15; const bool soft = (info >> 8) & 1;
+        const bool has2 = b2 < NB;
+        const int r0 = njrows + 3 * lane;
+        float n[3] = {cd[3], cd[4], cd[5]};
+        float c1[3] = {cd[0] - S.bpos[b1][0], cd[1] - S.bpos[b1][1], cd[2] - S.bpos[b1][2]};
+        float c2[3] = {0, 0, 0};
+        if (has2) { c2[0] = cd[0] - S.bpos[b2][0]; c2[1] = cd[1] - S.bpos[b2][1]; c2[2] = cd[2] - S.bpos[b2][2]; }
+        float t1[3], t2[3]; planeSpace(n, t1, t2);
+        const float erp_ = soft ? 0.4f : cfg.erp;
+        float depth = cd[6]; if (depth < 0) depth = 0;
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+          const float* d = (r == 0) ? n : (r == 1 ? t1 : t2);
+          float* Jr = S.rowJ[r0 + r]; float* Sr = S.rowS[r0 + r];
+          float x[3]; cross3(x, c1, d);
+          Jr[0] = d[0]; Jr[1] = d[1]; Jr[2] = d[2]; Jr[3] = x[0]; Jr[4] = x[1]; Jr[5] = x[2];
+          if (has2) { cross3(x, c2, d); Jr[6] = -d[0]; Jr[7] = -d[1]; Jr[8] = -d[2]; Jr[9] = -x[0]; Jr[10] = -x[1]; Jr[11] = -x[2]; }
+          else { Jr[6] = 0; Jr[7] = 0; Jr[8] = 0; Jr[9] = 0; Jr[10] = 0; Jr[11] = 0; }
+          Sr[RS_LAM] = 0.0f;
+          if (r == 0) { Sr[RS_C] = fps * erp_ * depth; Sr[RS_ADCFM] = soft ? 0.005f : cfg.cfm; Sr[RS_LO] = 0.0f; Sr[RS_HI] = CUDART_INF_F; Sr[RS_HDR] = __int_as_float(b1 | (b2 << 4) | (255 << 8)); }
+          else { Sr[RS_C] = 0.0f; Sr[RS_ADCFM] = cfg.cfm; Sr[RS_LO] = -cfg.mu; Sr[RS_HI] = cfg.mu; Sr[RS_HDR] = __int_as_float(b1 | (b2 << 4) | (r0 << 8)); }
+        }
+      }
+      __syncwarp();
+
+      // ------------------------------------------------------------ rhs, Ad (lane = row)
+      for (int r = lane; r < m_total; r += 32) {
+        const float* Jr = S.rowJ[r]; float* Sr = S.rowS[r];
+        const int hdr = __float_as_int(Sr[RS_HDR]);
+        const int b1 = hdr & 15, b2 = (hdr >> 4) & 15;
+        const float* t1 = S.btmp[b1]; const float* i1 = S.binvI[b1];
+        float s = Jr[0] * t1[0] + Jr[1] * t1[1] + Jr[2] * t1[2] + Jr[3] * t1[3] + Jr[4] * t1[4] + Jr[5] * t1[5];
+        float ax = i1[0] * Jr[3] + i1[1] * Jr[4] + i1[2] * Jr[5], ay = i1[1] * Jr[3] + i1[3] * Jr[4] + i1[4] * Jr[5], az = i1[2] * Jr[3] + i1[4] * Jr[4] + i1[5] * Jr[5];
+        float diag = i1[6] * (Jr[0] * Jr[0] + Jr[1] * Jr[1] + Jr[2] * Jr[2]) + (ax * Jr[3] + ay * Jr[4] + az * Jr[5]);
+        if (b2 < NB) {
+          const float* t2 = S.btmp[b2]; const float* i2 = S.binvI[b2];
+          s += Jr[6] * t2[0] + Jr[7] * t2[1] + Jr[8] * t2[2] + Jr[9] * t2[3] + Jr[10] * t2[4] + Jr[11] * t2[5];
+          ax = i2[0] * Jr[9] + i2[1] * Jr[10] + i2[2] * Jr[11]; ay = i2[1] * Jr[9] + i2[3] * Jr[10] + i2[4] * Jr[11]; az = i2[2] * Jr[9] + i2[4] * Jr[10] + i2[5] * Jr[11];
+          diag += i2[6] * (Jr[6] * Jr[6] + Jr[7] * Jr[7] + Jr[8] * Jr[8]) + (ax * Jr[9] + ay * Jr[10] + az * Jr[11]);
+        }
+        const float cfm_h = Sr[RS_ADCFM] * fps;
+        const float Ad = cfg.sor_w / (diag + cfm_h);
+        Sr[RS_RHS] = Sr[RS_C] * fps - s;
+        Sr[RS_AD] = Ad;
+        Sr[RS_ADCFM] = Ad * cfm_h;
+      }
+
+      // ------------------------------------------------------------ constraint order per island (quickstep.cpp SOR_LCP)
+      int cntN[NISL], cntF[NISL];
+#pragma unroll
+      for (int L = 0; L < NISL; L++) { cntN[L] = 0; cntF[L] = 0; }
+      for (int r0 = 0; r0 < m_total; r0 += 32) {
+        const int r = r0 + lane; const bool valid = r < m_total;
+        int lab = -1, fric = 0;
+        if (valid) { int hdr = __float_as_int(S.rowS[r][RS_HDR]); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
+#pragma unroll
+          for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L]; }
+#pragma unroll
+        for (int L = 0; L < NISL; L++) {
+          cntN[L] += __popc(__ballot_sync(FULLMASK, valid && lab == L && !fric));
+          cntF[L] += __popc(__ballot_sync(FULLMASK, valid && lab == L && fric));
+        }
+      }
+      int offL[NISL], mL[NISL], baseL[NISL];
+      const int nshuf = (cfg.pgs_iters + 7) >> 3;
+      { int acc = 0, draws = 0;
+#pragma unroll
+        for (int L = 0; L < NISL; L++) { mL[L] = cntN[L] + cntF[L]; offL[L] = acc; acc += mL[L]; baseL[L] = draws; draws += nshuf * max(mL[L] - 1, 0); }
+        if (lane == 0) { S.aux[8] = __int_as_float(draws); S.c.n_rows = m_total; }
+      }
+      {
+        int pN[NISL], pF[NISL];
+#pragma unroll
+        for (int L = 0; L < NISL; L++) { pN[L] = 0; pF[L] = 0; }
+        const unsigned lt = (1u << lane) - 1u;
+        for (int r0 = 0; r0 < m_total; r0 += 32) {
+          const int r = r0 + lane; const bool valid = r < m_total;
+          int lab = -1, fric = 0;
+          if (valid) { int hdr = __float_as_int(S.rowS[r][RS_HDR]); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
+#pragma unroll
+            for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L]; }
+#pragma unroll
+          for (int L = 0; L < NISL; L++) {
+            unsigned bN = __ballot_sync(FULLMASK, valid && lab == L && !fric);
+            unsigned bF = __ballot_sync(FULLMASK, valid && lab == L && fric);
+            if (valid && lab == L) {
+              int p = fric ? (offL[L] + mL[L] - 1 - (pF[L] + __popc(bF & lt))) : (offL[L] + pN[L] + __popc(bN & lt));
+              S.order[p] = (unsigned char)r;
+            }
+            pN[L] += __popc(bN); pF[L] += __popc(bF);
+          }
+        }
+      }
+      // my island (as a body lane)
+      int my_off = 0, my_m = 0, my_base = 0; bool leader = false;
+      if (body_lane) {
+        const int g = body_group(lane);
+        int lab = 0;
+#pragma unroll
+        for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L];
+#pragma unroll
+        for (int L = 0; L < NISL; L++) if (lab == L) { my_off = offL[L]; my_m = mL[L]; my_base = baseL[L]; }
+        const int first_body = (lab == 0) ? 0 : (lab == 1 ? 4 : (lab == 2 ? 5 : (lab == 3 ? 10 : 11)));
+        leader = lane == first_body;
+      }
+      int maxm = 0;
+#pragma unroll
+      for (int L = 0; L < NISL; L++) maxm = max(maxm, mL[L]);
+      __syncwarp();
+
+      // ------------------------------------------------------------ PGS / SOR sweeps
+      float fc[6] = {0, 0, 0, 0, 0, 0};
+      const uint32_t seed0 = S.c.lcg_seed;
+      for (int it = 0; it < cfg.pgs_iters; it++) {
+        if ((it & 7) == 0) {
+          if (leader && my_m > 1) {  // Fisher-Yates with ODE's dRandInt, this island's slice of the env's LCG stream
+            uint32_t sd = lcg_jump(seed0, (uint32_t)(my_base + (it >> 3) * (my_m - 1)));
+            for (int i = 1; i < my_m; i++) {
+              int sw = lcg_randint(sd, (uint32_t)(i + 1));
+              unsigned char a = S.order[my_off + i], b = S.order[my_off + sw];
+              S.order[my_off + i] = b; S.order[my_off + sw] = a;
+            }
+          }
+          __syncwarp();
+        }
+        for (int k = 0; k < maxm; k++) {
+          const bool act = body_lane && k < my_m;
+          const int row = act ? S.order[my_off + k] : 0;
+          const float* Sr = S.rowS[row];
+          const int hdr = __float_as_int(Sr[RS_HDR]);
+          const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
+          const bool is1 = act && lane == b1, is2 = act && lane == b2;
+          const bool mine = is1 || is2;
+          const float* Jm = S.rowJ[row] + (is2 ? 6 : 0);
+          float J0 = 0, J1 = 0, J2 = 0, J3 = 0, J4 = 0, J5 = 0, part = 0;
+          float rhs = 0, Ad = 0, Adcfm = 0, lo = 0, hi = 0, lam = 0;
+          if (mine) {
+            J0 = Jm[0]; J1 = Jm[1]; J2 = Jm[2]; J3 = Jm[3]; J4 = Jm[4]; J5 = Jm[5];
+            part = J0 * fc[0] + J1 * fc[1] + J2 * fc[2] + J3 * fc[3] + J4 * fc[4] + J5 * fc[5];
+            rhs = Sr[RS_RHS]; Ad = Sr[RS_AD]; Adcfm = Sr[RS_ADCFM]; lo = Sr[RS_LO]; hi = Sr[RS_HI]; lam = Sr[RS_LAM];
+            if (fidx != 255) { hi = fabsf(hi * S.rowS[fidx][RS_LAM]); lo = -hi; }
+          }
+          const int partner = is1 ? (b2 < NB ? b2 : lane) : (is2 ? b1 : lane);
+          float other = __shfl_sync(FULLMASK, part, partner);
+          __syncwarp();
+          if (mine) {
+            if (is1 && b2 >= NB) other = 0.0f;
+            const float sum = is1 ? (part + other) : (other + part);
+            float delta = Ad * (rhs - sum) - lam * Adcfm;
+            float nl = lam + delta;
+            if (nl < lo) { delta = lo - lam; nl = lo; }
+            else if (nl > hi) { delta = hi - lam; nl = hi; }
+            if (is1) S.rowS[row][RS_LAM] = nl;
+            const float dm = delta * invMass;
+            fc[0] += dm * J0; fc[1] += dm * J1; fc[2] += dm * J2;
+            const float ax = iI[0] * J3 + iI[1] * J4 + iI[2] * J5, ay = iI[1] * J3 + iI[3] * J4 + iI[4] * J5, az = iI[2] * J3 + iI[4] * J4 + iI[5] * J5;
+            fc[3] += delta * ax; fc[4] += delta * ay; fc[5] += delta * az;
+          }
+          __syncwarp();
+        }
+      }
+      if (lane == 0) S.c.lcg_seed = lcg_jump(seed0, (uint32_t)__float_as_int(S.aux[8]));
+
+      // ------------------------------------------------------------ velocity update + dxStepBody
+      if (body_lane) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) { lvel[k] += h * fc[k]; avel[k] += h * fc[3 + k]; }
+        const float hm = h * invMass;
+        float ht[3] = {tacc[0] * h, tacc[1] * h, tacc[2] * h};
+#pragma unroll
+        for (int k = 0; k < 3; k++) lvel[k] += hm * facc[k];
+        avel[0] += iI[0] * ht[0] + iI[1] * ht[1] + iI[2] * ht[2];
+        avel[1] += iI[1] * ht[0] + iI[3] * ht[1] + iI[4] * ht[2];
+        avel[2] += iI[2] * ht[0] + iI[4] * ht[1] + iI[5] * ht[2];
+#pragma unroll
+        for (int k = 0; k < 3; k++) pos[k] += h * lvel[k];
+        float dq[4];
+        dq[0] = 0.5f * (-avel[0] * q[1] - avel[1] * q[2] - avel[2] * q[3]);
+        dq[1] = 0.5f * (avel[0] * q[0] + avel[1] * q[3] - avel[2] * q[2]);
+        dq[2] = 0.5f * (-avel[0] * q[3] + avel[1] * q[0] + avel[2] * q[1]);
+        dq[3] = 0.5f * (avel[0] * q[2] - avel[1] * q[1] + avel[2] * q[0]);
+#pragma unroll
+        for (int k = 0; k < 4; k++) q[k] += h * dq[k];
+        float l = q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3];
+        l = 1.0f / sqrtf(l);
+#pragma unroll
+        for (int k = 0; k < 4; k++) q[k] *= l;
+        quatToR(R, q);
+#pragma unroll
+        for (int k = 0; k < 3; k++) { facc[k] = 0; tacc[k] = 0; }
+      }
+      publish_body(S, lane, pos, q, R, lvel, avel);
+      __syncwarp();
+
+      // ------------------------------------------------------------ Rover_1::next_step, first half (src/rover_1.cc:480-494)
+      joint_readouts(S, lane);
+      if (lane < 2) {  // FT_sensor::Update (ode/ft_sensor.cc:58-88); lane 0 front (main, front fork), lane 1 rear (boggie, rear fork)
+        const int A = lane == 0 ? 0 : 3, B = lane == 0 ? 4 : 5;
+        float rA[3], rB[3], pA[3], pB[3], vA[3], vB[3], t3[3];
+        mulRv(rA, S.bR[A], M.ft_ocA[lane]); mulRv(rB, S.bR[B], M.ft_ocB[lane]);
+        for (int k = 0; k < 3; k++) { pA[k] = rA[k] + S.bpos[A][k]; pB[k] = rB[k] + S.bpos[B][k]; }
+        cross3(t3, &S.bvel[A][3], rA); for (int k = 0; k < 3; k++) vA[k] = S.bvel[A][k] + t3[k];
+        cross3(t3, &S.bvel[B][3], rB); for (int k = 0; k < 3; k++) vB[k] = S.bvel[B][k] + t3[k];
+        const float Kl[3] = {2e4f, 2e4f, 1e5f};
+        float F[3], T[3];
+        for (int k = 0; k < 3; k++) F[k] = Kl[k] * (pB[k] - pA[k]) + 5e2f * (vB[k] - vA[k]);
+        const float* qA = S.bq[A]; const float* qB = S.bq[B];
+        float n2 = qA[0] * qA[0] + qA[1] * qA[1] + qA[2] * qA[2] + qA[3] * qA[3];
+        float qi[4] = {qA[0] / n2, -qA[1] / n2, -qA[2] / n2, -qA[3] / n2};
+        float qr[4]; qmul(qr, qB, qi);
+        float n = sqrtf(qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
+        float angle, axis[3];
+        if (n != 0.0f) { angle = 2.0f * atan2f(n, fabsf(qr[0])); if (qr[0] < 0.0f) n = -n; axis[0] = qr[1] / n; axis[1] = qr[2] / n; axis[2] = qr[3] / n; }
+        else { angle = 0; axis[0] = 1; axis[1] = 0; axis[2] = 0; }
+        for (int k = 0; k < 3; k++) T[k] = angle * 1e3f * axis[k] + 1.0f * (S.bvel[B][3 + k] - S.bvel[A][3 + k]);
+        for (int k = 0; k < 3; k++) { S.ftraw[lane * 6 + k] = F[k]; S.ftraw[lane * 6 + 3 + k] = T[k]; }
+      }
+      __syncwarp();
+      if (lane == 0 || lane == 3 || lane == 4 || lane == 5) {  // dBodyAddForceAtRelPos / dBodyAddTorque on A (+) and B (-)
+        const int s = (lane == 0 || lane == 4) ? 0 : 1;
+        const bool isA = (lane == 0 || lane == 3);
+        const float sg = isA ? 1.0f : -1.0f;
+        const float* oc = isA ? M.ft_ocA[s] : M.ft_ocB[s];
+        float F[3] = {sg * S.ftraw[s * 6 + 0], sg * S.ftraw[s * 6 + 1], sg * S.ftraw[s * 6 + 2]};
+        float T[3] = {sg * S.ftraw[s * 6 + 3], sg * S.ftraw[s * 6 + 4], sg * S.ftraw[s * 6 + 5]};
+        float pr[3]; mulRv(pr, R, oc);
+        float cx[3]; cross3(cx, pr, F);
+        for (int k = 0; k < 3; k++) { facc[k] += F[k]; tacc[k] += cx[k]; }
+        for (int k = 0; k < 3; k++) tacc[k] += T[k];
+      }
+      if (lane < 12) {  // 12 biquads in place (Filters/cpp/filters.cc:137-144), fp64 state
+        const double Cy1 = M.filt_c[0], Cy2 = M.filt_c[1], Cx0 = M.filt_c[2];
+        double* f = S.c.filt[lane];
+        const double x = (double)S.ftraw[lane];
+        const double y = Cy1 * f[0] + Cy2 * f[1] + Cx0 * x + (2 * Cx0) * f[2] + Cx0 * f[3];
+        f[1] = f[0]; f[0] = y; f[3] = f[2]; f[2] = x;
+        S.c.ft[lane] = (float)y;
+      }
+      __syncwarp();
+      if (lane == 0) {
+        Ctrl& c = S.c;
+        c.ic_clock += (double)cfg.dt;
+        if (c.ic_activated && c.ic_clock >= (double)c.ic_period) {
+          const double delta_t = c.ic_clock;
+          c.tick++;
+          bool park = false;
+          if (cfg.controller == TFODE_CTRL_RANDOM) {
+            uint32_t r[4]; philox(cfg.seed, env_global, c.episode, c.tick, 1, r);
+            c.steering_rate = fmin(fmax(-15.0, (double)u11(r[0]) * 15.0), 15.0);
+            c.boggie_torque = fmin(fmax(-25.0, (double)u11(r[1]) * 25.0), 25.0);
+          } else if (cfg.controller == TFODE_CTRL_MLP) {
+            // _ComputeReward (src/rover_1_tf.cc:80-108)
+            float np[3]; mulRv(np, S.bR[0], M.getpos_rel);
+            np[0] += S.bpos[0][0]; np[1] += S.bpos[0][1]; np[2] += S.bpos[0][2];
+            double reward = ((double)np[0] - c.last_pos[0]) * (25. / delta_t);
+            reward -= fabs(c.boggie_torque) / 25.0 * 0.5;
+            if (c.fork_collision) { reward -= 1; c.fork_collision = 0; }
+            for (int k = 0; k < 3; k++) c.last_pos[k] = (double)np[k];
+            c.total_reward += reward; c.last_reward = reward;
+            float cur[17]; get_state17(S, cur);
+            if (c.has_last_state) {
+              if (c.pending_valid) append_transition(P, c, env_global, false, 0.0f);
+              for (int i = 0; i < 17; i++) c.pending[i] = c.last_state[i];
+              c.pending[17] = (float)c.steering_rate; c.pending[18] = (float)c.boggie_torque; c.pending[19] = (float)reward;
+              for (int i = 0; i < 17; i++) c.pending[20 + i] = cur[i];
+              c.pending_valid = 1;
+            }
+            uint32_t r[4]; philox(cfg.seed, env_global, c.episode, c.tick, 1, r);
+            const double draw = ((double)u11(r[0]) + 1) / 2;
+            if (cfg.exploration && ((!c.explore && draw > 0.8) || (c.explore && draw > 0.7))) {
+              c.explore = !c.explore;
+              if (c.explore) { c.steering_rate = (double)u11(r[1]) * 15.0; c.boggie_torque = (double)u11(r[2]) * 25.0; }
+            }
+            if (!cfg.exploration || !c.explore) {
+              const float scaling[17] = {90, 45, 25, 25, 45, 100, 100, 100, 30, 30, 30, 100, 100, 100, 30, 30, 30};
+              float* in = P.policy_in + (size_t)env * 17;
+              for (int i = 0; i < 17; i++) in[i] = cur[i] / scaling[i];
+              int slot = atomicAdd(P.n_parked, 1);
+              P.parked_list[slot] = env;
+              park = true;
+            }
+            for (int i = 0; i < 17; i++) c.last_state[i] = cur[i];
+            c.has_last_state = 1;
+          } else if (cfg.controller == TFODE_CTRL_CRAWLER) {  // src/rover_1_crawlers.cc:40-77
+            const double ang = (double)(c.jq_angle[1] * 57.29577951308232f);
+            switch (c.cr_phase) {
+              case 1: c.boggie_torque += c.cr_dtorque_dt * delta_t; if (c.boggie_torque >= c.cr_amp) { c.boggie_torque = c.cr_amp; ++c.cr_phase; } break;
+              case 2: c.steering_rate = c.cr_rate; if (ang >= 45.0) { c.steering_rate = 0; ++c.cr_phase; } break;
+              case 3: c.boggie_torque -= c.cr_dtorque_dt * delta_t; if (c.boggie_torque <= -c.cr_amp) { c.boggie_torque = -c.cr_amp; ++c.cr_phase; } break;
+              case 4: c.steering_rate = -c.cr_rate; if (ang <= -45.0) { c.steering_rate = 0; c.cr_phase = 1; } break;
+            }
+          }
+          c.ic_clock = 0; c.ic_tick = 1;
+          c.parked = park ? 1 : 0;
+        } else c.ic_tick = 0;
+      }
+      __syncwarp();
+      if (S.c.parked == 1) break;  // hand the env to the policy kernel; part B runs in the next launch
+    } else {
+      // resumed after the policy kernel: TF_model::infer outputs are in policy_act (src/rover_1_tf.cc:184-185)
+      if (lane == 0) {
+        S.c.steering_rate = (double)S.c.policy_act[0] * 15.0;
+        S.c.boggie_torque = (double)S.c.policy_act[1] * 25.0;
+        S.c.parked = 0;
+      }
+      __syncwarp();
+    }
+
+    // ---------------------------------------------------------------- Rover_1::next_step, second half (src/rover_1.cc:496-502)
+    if (lane == 0) {
+      Ctrl& c = S.c;
+      // _UpdateWheelControl (:346-386)
+      const float gamma = c.jq_angle[1], dgamma = c.jq_rate[1];
+      const float wb = 0.58f, wt = 0.61f, rs = (float)c.robot_speed, wr = 0.105f, WMS = 7.4351f;
+      float diff[4], trans[4], min_speed = 0, adj;
+      const float tg = tanf(gamma / 2);
+      const bool crawl = cfg.crawling_mode || cfg.controller == TFODE_CTRL_CRAWLER;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        diff[i] = (i % 2 ? -1 : 1) * wt / wb * tg;
+        trans[i] = (i / 2 ? -1 : 1) * (-wb * tg + (i % 2 ? -1 : 1) * wt) * dgamma / 4;
+        if (crawl) { if (rs >= 0) min_speed = fmaxf(min_speed, -trans[i] / (1 + diff[i])); else min_speed = fminf(min_speed, -trans[i] / (1 + diff[i])); }
+      }
+      if (rs >= 0) adj = fmaxf(rs, min_speed); else adj = fminf(rs, min_speed);
+#pragma unroll
+      for (int i = 0; i < 4; i++) { if (rs >= 0) adj = fminf(adj, (WMS * wr - trans[i]) / (1 + diff[i])); else adj = fmaxf(adj, (-WMS * wr - trans[i]) / (1 + diff[i])); }
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        float W = (adj * (1 + diff[i]) + trans[i]) / wr;
+        W = fminf(fmaxf(-WMS, W), WMS);  // _ApplyWheelControl (:389-400)
+        c.W[i] = W;
+        float mt = 25.4f - 3.416228430014391f * fabsf(c.jq_rate[3 + i]);
+        if (mt >= 0) c.wheel_fmax[i] = mt;  // dParamFMax ignores negative values
+        c.wheel_vel[i] = W;
+      }
+      // Servo::set_desired_vel (ode/servo.cc:123-134) + Servo::next_step (:145-167)
+      const float vmax = (float)(15 * 0.017453292519943295), smin = (float)(-45 * 0.017453292519943295), smax = (float)(45 * 0.017453292519943295);
+      float vel = (float)(c.steering_rate * 0.017453292519943295);
+      vel = fmaxf(-vmax, vel); vel = fminf(vel, vmax);
+      if ((gamma <= smin && vel < 0) || (gamma >= smax && vel > 0)) vel = 0;
+      c.servo_vel = vel; c.servo_mode_vel = 1;
+      // _ApplyBoggieControl (:411-416): torque vector on the boggie (+) and the rear body (-)
+      const double bmax = (cfg.controller == TFODE_CTRL_CRAWLER) ? (double)c.cr_amp : 25.0;
+      const float tq = (float)fmin(fmax(-bmax, c.boggie_torque), bmax);
+      float ax[3]; mulRv(ax, S.bR[3], M.axis1[2]);
+      S.aux[0] = ax[0] * tq; S.aux[1] = ax[1] * tq; S.aux[2] = ax[2] * tq;
+    }
+    __syncwarp();
+    if (lane == 3) { tacc[0] += S.aux[0]; tacc[1] += S.aux[1]; tacc[2] += S.aux[2]; }
+    if (lane == 2) { tacc[0] += -S.aux[0]; tacc[1] += -S.aux[1]; tacc[2] += -S.aux[2]; }
+
+    // ---------------------------------------------------------------- termination test (rover_training_1.cc:141-143) + epilogue (:212-224)
+    if (lane == 0) {
+      Ctrl& c = S.c;
+      int reason = 0;
+      if (cfg.terminate) {
+        float p[3]; mulRv(p, S.bR[0], M.getpos_rel);
+        p[0] += S.bpos[0][0]; p[1] += S.bpos[0][1]; p[2] += S.bpos[0][2];
+        const double time = (double)((float)c.time_steps * cfg.dt);
+        const bool upside = S.bR[0][8] < 0;
+        if (time >= (double)cfg.timeout) reason = TFODE_TERM_TIMEOUT;
+        else if (cfg.y_max > 0 && fabs((double)p[1]) >= (double)cfg.y_max) reason = TFODE_TERM_Y_MAX;
+        else if ((cfg.x_goal_abs ? fabs((double)p[0]) : (double)p[0]) >= (double)cfg.x_goal) reason = TFODE_TERM_X_GOAL;
+        else if (cfg.check_upside_down && upside) reason = TFODE_TERM_UPSIDE_DOWN;
+        if (reason) {
+          if (c.pending_valid) {
+            float pen = 0;
+            if (cfg.y_max > 0 && fabs((double)p[1]) >= (double)cfg.y_max) pen = 2; else if (cfg.check_upside_down && upside) pen = 5;
+            append_transition(P, c, env_global, true, pen); c.pending_valid = 0;
+          }
+          c.last_ep_return = (float)c.total_reward; c.last_ep_x = p[0]; c.last_ep_y = p[1]; c.last_ep_steps = (int)c.time_steps;
+          c.done_call = 1; c.done_step = 1; c.term_reason = reason; c.episodes_done++;
+          if (!cfg.auto_reset) c.frozen = 1;
+        }
+      }
+      if (!reason) c.time_steps++;
+      S.aux[4] = __int_as_float(reason);
+    }
+    __syncwarp();
+    budget--;
+    if (__float_as_int(S.aux[4]) != 0 && cfg.auto_reset) {
+      const uint32_t ep = S.c.episode + 1;
+      __syncwarp();
+      reset_env(S, P, env_global, ep, lane, pos, q, lvel, avel, facc, tacc);
+      quatToR(R, q);
+      publish_body(S, lane, pos, q, R, lvel, avel);
+      __syncwarp();
+      joint_readouts(S, lane);
+      __syncwarp();
+    }
+  }
+
+  // ---------------------------------------------------------------- store the record
+  __syncwarp();
+  if (lane == 0) P.budget[env] = budget;
+  {
+    EnvRec* st = reinterpret_cast<EnvRec*>(&S.rowJ[0][0]);
+    if (lane < NB) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) { st->body[F_POS + k][lane] = pos[k]; st->body[F_LVEL + k][lane] = lvel[k]; st->body[F_AVEL + k][lane] = avel[k]; st->body[F_FACC + k][lane] = facc[k]; st->body[F_TACC + k][lane] = tacc[k]; }
+#pragma unroll
+      for (int k = 0; k < 4; k++) st->body[F_QUAT + k][lane] = q[k];
+    }
+    const uint32_t* cs = reinterpret_cast<const uint32_t*>(&S.c);
+    uint32_t* cd = reinterpret_cast<uint32_t*>(&st->c);
+    for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
+    __syncwarp();
+    const float4* src = reinterpret_cast<const float4*>(st);
+    float4* dst = reinterpret_cast<float4*>(grec);
+    constexpr int N4 = sizeof(EnvRec) / 16;
+    for (int i = lane; i < N4; i += 32) dst[i] = src[i];
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// reset kernel: construction of env records (initial create, tfode_batch_reset)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(WARPS_PER_CTA * 32) reset_kernel(const StepParams P, const int* env_ids, int n_ids, int first_time) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int idx = blockIdx.x * WARPS_PER_CTA + wid;
+  if (idx >= n_ids) return;
+  const int env = env_ids ? env_ids[idx] : idx;
+  if (env < 0 || env >= P.n_envs) return;
+  WarpSm& S = reinterpret_cast<WarpSm*>(smem_raw)[wid];
+  EnvRec* grec = P.rec + env;
+  {
+    const uint32_t* cs = reinterpret_cast<const uint32_t*>(&grec->c);
+    uint32_t* cd = reinterpret_cast<uint32_t*>(&S.c);
+    for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = first_time ? 0u : cs[i];
+  }
+  __syncwarp();
+  const uint32_t ep = first_time ? 0u : S.c.episode + 1;
+  if (lane == 0) { S.c.done_call = 0; S.c.frozen = 0; }
+  float pos[3], q[4], R[9], lvel[3], avel[3], facc[3], tacc[3];
+  reset_env(S, P, (uint32_t)(P.cfg.env_id_offset + env), ep, lane, pos, q, lvel, avel, facc, tacc);
+  if (lane == 0) { S.c.frozen = 0; S.c.parked = 0; }
+  quatToR(R, q);
+  publish_body(S, lane, pos, q, R, lvel, avel);
+  __syncwarp();
+  joint_readouts(S, lane);
+  __syncwarp();
+  if (lane < NB) {
+    for (int k = 0; k < 3; k++) { grec->body[F_POS + k][lane] = pos[k]; grec->body[F_LVEL + k][lane] = 0; grec->body[F_AVEL + k][lane] = 0; grec->body[F_FACC + k][lane] = 0; grec->body[F_TACC + k][lane] = 0; }
+    for (int k = 0; k < 4; k++) grec->body[F_QUAT + k][lane] = q[k];
+  }
+  {
+    const uint32_t* cs = reinterpret_cast<const uint32_t*>(&S.c);
+    uint32_t* cd = reinterpret_cast<uint32_t*>(&grec->c);
+    for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
+  }
+  if (lane == 0) P.budget[env] = 0;
+}
+
+// observation / bodies gathers (thread per env)
+__global__ void observe_kernel(const EnvRec* rec, int n, float* obs17, float* reward, uint8_t* done, int32_t* ncont) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const EnvRec& r = rec[e];
+  if (obs17) {
+    float q[4] = {r.body[F_QUAT + 0][0], r.body[F_QUAT + 1][0], r.body[F_QUAT + 2][0], r.body[F_QUAT + 3][0]};
+    float R[9]; quatToR(R, q);
+    float vx0 = R[0], vx1 = R[3], vx2 = R[6];
+    float direction = asinf(vx1) * 57.29577951308232f;
+    if (vx0 < 0) direction = (vx1 > 0 ? 1.0f : -1.0f) * 180.0f - direction;
+    float* o = obs17 + (size_t)e * 17;
+    o[0] = direction; o[1] = r.c.jq_angle[1] * 57.29577951308232f; o[2] = asinf(R[7]) * 57.29577951308232f;
+    o[3] = asinf(-vx2) * 57.29577951308232f; o[4] = r.c.jq_angle[2] * 57.29577951308232f;
+    for (int i = 0; i < 12; i++) o[5 + i] = r.c.ft[i];
+  }
+  if (reward) reward[e] = (float)r.c.last_reward;
+  if (done) done[e] = (uint8_t)(r.c.done_call != 0);
+  if (ncont) ncont[e] = r.c.n_contacts;
+}
+__global__ void bodies_kernel(const EnvRec* rec, int n, float* out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * NB) return;
+  const int e = i / NB, b = i - e * NB;
+  const EnvRec& r = rec[e];
+  float* o = out + (size_t)i * 13;
+  for (int k = 0; k < 13; k++) o[k] = r.body[k][b];
+}
+__global__ void set_actions_kernel(EnvRec* rec, int n, const float* act, float bmax) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  rec[e].c.steering_rate = fmin(fmax(-15.0, (double)act[e * 2]), 15.0);          // SetSteeringRate, src/rover_1.cc:326-329
+  rec[e].c.boggie_torque = fmin(fmax(-(double)bmax, (double)act[e * 2 + 1]), (double)bmax);  // SetBoggieTorque :338-341
+}
+
+// ------------------------------------------------------------------------------------------------
+// fp32 policy kernel (TF_model<float>::infer for the parked envs): 17 -> 512 relu -> 512 relu -> 2 tanh
+// ------------------------------------------------------------------------------------------------
+constexpr int POL_ROWS = 8;
+__global__ void __launch_bounds__(256) policy_fp32_kernel(const float* __restrict__ in_all, const int* __restrict__ list, const int* __restrict__ n_list, int m_direct,
+                                                          const float* __restrict__ W1, const float* __restrict__ b1, const float* __restrict__ W2, const float* __restrict__ b2,
+                                                          const float* __restrict__ W3, const float* __restrict__ b3, EnvRec* rec, float* act_direct) {
+  __shared__ float x[POL_ROWS][17];
+  __shared__ float h1[POL_ROWS][512];
+  __shared__ float h2[POL_ROWS][512];
+  const int m = list ? *n_list : m_direct;
+  const int row0 = blockIdx.x * POL_ROWS;
+  if (row0 >= m) return;
+  const int nr = min(POL_ROWS, m - row0);
+  const int t = threadIdx.x;
+  for (int i = t; i < nr * 17; i += 256) { int r = i / 17, k = i - r * 17; int src = list ? list[row0 + r] : (row0 + r); x[r][k] = in_all[(size_t)src * 17 + k]; }
+  __syncthreads();
+  for (int j = t; j < 512; j += 256) {
+    float acc[POL_ROWS];
+#pragma unroll
+    for (int r = 0; r < POL_ROWS; r++) acc[r] = b1[j];
+    for (int i = 0; i < 17; i++) { float w = W1[i * 512 + j];
+#pragma unroll
+      for (int r = 0; r < POL_ROWS; r++) acc[r] += x[r][i] * w; }
+#pragma unroll
+    for (int r = 0; r < POL_ROWS; r++) h1[r][j] = acc[r] > 0 ? acc[r] : 0;
+  }
+  __syncthreads();
+  for (int j = t; j < 512; j += 256) {
+    float acc[POL_ROWS];
+#pragma unroll
+    for (int r = 0; r < POL_ROWS; r++) acc[r] = b2[j];
+    for (int i = 0; i < 512; i++) { float w = W2[i * 512 + j];
+#pragma unroll
+      for (int r = 0; r < POL_ROWS; r++) acc[r] += h1[r][i] * w; }
+#pragma unroll
+    for (int r = 0; r < POL_ROWS; r++) h2[r][j] = acc[r] > 0 ? acc[r] : 0;
+  }
+  __syncthreads();
+  // layer 3: warp w handles rows w, w+8; sequential-order-independent tree sum
+  const int lane = t & 31, w = t >> 5;
+  for (int r = w; r < nr; r += 8) {
+    float s0 = 0, s1 = 0;
+    for (int i = lane; i < 512; i += 32) { s0 += h2[r][i] * W3[i * 2 + 0]; s1 += h2[r][i] * W3[i * 2 + 1]; }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) { s0 += __shfl_xor_sync(FULLMASK, s0, d); s1 += __shfl_xor_sync(FULLMASK, s1, d); }
+    if (lane == 0) {
+      float a0 = tanhf(s0 + b3[0]), a1 = tanhf(s1 + b3[1]);
+      if (list) { EnvRec& e = rec[list[row0 + r]]; e.c.policy_act[0] = a0; e.c.policy_act[1] = a1; e.c.parked = 2; }
+      else { act_direct[(size_t)(row0 + r) * 2] = a0; act_direct[(size_t)(row0 + r) * 2 + 1] = a1; }
+    }
+  }
+}
+__global__ void zero_int_kernel(int* p) { *p = 0; }
+
+}  // namespace tfode

@@ -1,0 +1,174 @@
+"""Python host mirror of the reference's stepping interface, over the C ABI (include/tfode_batch.h).
+
+`RoverBatch` plays the role of `ode::Environment` + `robot::Rover_1*` for N environments at once:
+`step(n)` is n x { env.next_step(dt); robot.next_step(dt) } of the scene lambdas
+(src/rover_training_1.cc:127-146).  There is no CPU implementation behind this class: if
+libtfode_b200.so is missing or no B200 is visible, construction raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libtfode_b200.so")
+_LIB = None
+
+EXPORTS = [
+    "tfode_batch_config_default", "tfode_batch_create", "tfode_batch_destroy", "tfode_last_error",
+    "tfode_batch_set_stream", "tfode_batch_reset", "tfode_batch_set_actions", "tfode_batch_set_speed",
+    "tfode_batch_load_policy", "tfode_batch_step", "tfode_batch_observe", "tfode_batch_get_bodies",
+    "tfode_batch_drain_transitions", "tfode_batch_rollout_host", "tfode_batch_get_state",
+    "tfode_batch_set_state", "tfode_batch_launch_count", "tfode_batch_n_envs", "tfode_batch_sync",
+    "tfode_policy_infer",
+]
+
+
+class TfodeError(RuntimeError):
+    pass
+
+
+def load_library():
+    """dlopen the C-ABI library. Raises if it was not built (run tf_ode_b200/csrc/build.sh)."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise TfodeError("%s not found: build it with tf_ode_b200/csrc/build.sh (no CPU fallback exists)" % LIB_PATH)
+    L = C.CDLL(LIB_PATH)
+    vp, i32, i64 = C.c_void_p, C.c_int, C.c_int64
+    L.tfode_batch_config_default.argtypes = [C.POINTER(abi.BatchConfig), i32]
+    L.tfode_batch_create.argtypes = [C.POINTER(abi.BatchConfig), C.POINTER(vp)]
+    L.tfode_batch_destroy.argtypes = [vp]
+    L.tfode_batch_destroy.restype = None
+    L.tfode_last_error.argtypes = [vp]
+    L.tfode_last_error.restype = C.c_char_p
+    L.tfode_batch_set_stream.argtypes = [vp, vp]
+    L.tfode_batch_reset.argtypes = [vp, vp, i32]
+    L.tfode_batch_set_actions.argtypes = [vp, vp]
+    L.tfode_batch_set_speed.argtypes = [vp, vp]
+    L.tfode_batch_load_policy.argtypes = [vp, vp, C.c_size_t]
+    L.tfode_batch_step.argtypes = [vp, i32]
+    L.tfode_batch_observe.argtypes = [vp, vp, vp, vp, vp]
+    L.tfode_batch_get_bodies.argtypes = [vp, vp]
+    L.tfode_batch_drain_transitions.argtypes = [vp, vp, i32, C.POINTER(i32)]
+    L.tfode_batch_rollout_host.argtypes = [vp, vp, i32, vp, vp, vp]
+    L.tfode_batch_get_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
+    L.tfode_batch_set_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
+    L.tfode_batch_launch_count.argtypes = [vp]
+    L.tfode_batch_launch_count.restype = i64
+    L.tfode_batch_n_envs.argtypes = [vp]
+    L.tfode_batch_sync.argtypes = [vp]
+    L.tfode_policy_infer.argtypes = [vp, vp, i32, vp]
+    _LIB = L
+    return L
+
+
+def _hp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _dp(t):
+    """device pointer of a torch tensor (or None)."""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous()
+    return C.c_void_p(t.data_ptr())
+
+
+def glorot_policy(seed=7):
+    """Glorot-uniform 17-512-512-2 actor with zero biases (no trained model ships), Keras [in,out] layout."""
+    rng = np.random.RandomState(seed)
+    out = []
+    for fi, fo in ((17, 512), (512, 512), (512, 2)):
+        lim = np.sqrt(6.0 / (fi + fo))
+        out.append(rng.uniform(-lim, lim, size=(fi, fo)).astype(np.float32).ravel())
+        out.append(np.zeros(fo, np.float32))
+    w = np.concatenate(out)
+    assert w.size == abi.POLICY_NFLOATS
+    return w
+
+
+class RoverBatch:
+    def __init__(self, cfg, stream=None):
+        self.L = load_library()
+        self.cfg = cfg
+        self.n = cfg.n_envs
+        h = C.c_void_p()
+        rc = self.L.tfode_batch_create(C.byref(cfg), C.byref(h))
+        if rc != 0:
+            raise TfodeError("tfode_batch_create failed (%d): %s" % (rc, self.L.tfode_last_error(None).decode()))
+        self.h = h
+        if stream is not None:
+            self._ck(self.L.tfode_batch_set_stream(self.h, C.c_void_p(stream)))
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TfodeError("tfode call failed (%d): %s" % (rc, self.L.tfode_last_error(self.h).decode()))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.tfode_batch_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # --- the reference-facing calls -------------------------------------------------------------
+    def step(self, n=1):
+        self._ck(self.L.tfode_batch_step(self.h, n))
+
+    def reset(self, ids=None):
+        if ids is None:
+            self._ck(self.L.tfode_batch_reset(self.h, None, 0))
+        else:
+            ids = np.ascontiguousarray(ids, dtype=np.int32)
+            self._ck(self.L.tfode_batch_reset(self.h, _hp(ids), ids.size))
+
+    def load_policy(self, w):
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        self._ck(self.L.tfode_batch_load_policy(self.h, _hp(w), w.size))
+
+    def set_actions(self, actions_dev):
+        self._ck(self.L.tfode_batch_set_actions(self.h, _dp(actions_dev)))
+
+    def set_speed(self, speed_dev):
+        self._ck(self.L.tfode_batch_set_speed(self.h, _dp(speed_dev)))
+
+    def observe(self, obs=None, reward=None, done=None, ncontacts=None):
+        self._ck(self.L.tfode_batch_observe(self.h, _dp(obs), _dp(reward), _dp(done), _dp(ncontacts)))
+
+    def get_bodies(self, out_dev):
+        self._ck(self.L.tfode_batch_get_bodies(self.h, _dp(out_dev)))
+
+    def drain_transitions(self, out_dev, max_rows):
+        n = C.c_int(0)
+        self._ck(self.L.tfode_batch_drain_transitions(self.h, _dp(out_dev), max_rows, C.byref(n)))
+        return n.value
+
+    def rollout_host(self, actions, n_substeps, obs, reward, done):
+        """Host-buffer round trip (numpy arrays): H2D actions -> n steps -> D2H observations."""
+        self._ck(self.L.tfode_batch_rollout_host(self.h, _hp(actions), n_substeps, _hp(obs), _hp(reward), _hp(done)))
+
+    def policy_infer(self, obs_scaled_dev, act_dev):
+        self._ck(self.L.tfode_policy_infer(self.h, _dp(obs_scaled_dev), obs_scaled_dev.shape[0], _dp(act_dev)))
+
+    def get_state(self, env=0):
+        s = abi.EnvState()
+        self._ck(self.L.tfode_batch_get_state(self.h, env, C.byref(s)))
+        return s
+
+    def set_state(self, env, s):
+        self._ck(self.L.tfode_batch_set_state(self.h, env, C.byref(s)))
+
+    def sync(self):
+        self._ck(self.L.tfode_batch_sync(self.h))
+
+    @property
+    def launch_count(self):
+        return self.L.tfode_batch_launch_count(self.h)
