@@ -125,7 +125,7 @@ typedef struct TfodeBatchConfig {
   float hf_pos[3];          /* geom position (world) */
 
   uint64_t seed;            /* Philox key (20260411) */
-  int32_t max_contacts;     /* per-env contact capacity (<= 32); extra contacts are dropped in generation order */
+  int32_t max_contacts;     /* per-env contact capacity (1..24); extra contacts are dropped in generation order */
   int32_t transition_capacity; /* rows in the transition ring (0 = 4*n_envs) */
 } TfodeBatchConfig;
 

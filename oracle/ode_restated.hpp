@@ -28,30 +28,27 @@
 #include <limits>
 #include <vector>
 
+#include "../include/tfode_numerics.h"
+
 namespace ode_restated {
 
 template <class T> inline T inf() { return std::numeric_limits<T>::infinity(); }
 
 // ---------------------------------------------------------------- vec helpers
-template <class T> inline T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
-template <class T> inline void cross3(T* r, const T* a, const T* b) {
-  r[0] = a[1] * b[2] - a[2] * b[1];
-  r[1] = a[2] * b[0] - a[0] * b[2];
-  r[2] = a[0] * b[1] - a[1] * b[0];
-}
+// The fma placement of dot/cross/matrix-vector products is part of the numerics contract
+// (include/tfode_numerics.h); everything else below is plain IEEE arithmetic in source order.
+template <class T> inline T dot3(const T* a, const T* b) { return tfn::dot3(a, b); }
+template <class T> inline void cross3(T* r, const T* a, const T* b) { tfn::cross3(r, a, b); }
 template <class T> inline void set3(T* r, T x, T y, T z) { r[0] = x; r[1] = y; r[2] = z; }
 template <class T> inline void copy3(T* r, const T* a) { r[0] = a[0]; r[1] = a[1]; r[2] = a[2]; }
 // R is 3x3 row-major (ODE pads rows to 4; the padding carries no arithmetic).
-template <class T> inline void mulRv(T* r, const T* R, const T* v) {  // dMultiply0_331
-  T a = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
-  T b = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
-  T c = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
-  r[0] = a; r[1] = b; r[2] = c;
-}
-template <class T> inline void mulRtv(T* r, const T* R, const T* v) {  // dMultiply1_331
-  T a = R[0] * v[0] + R[3] * v[1] + R[6] * v[2];
-  T b = R[1] * v[0] + R[4] * v[1] + R[7] * v[2];
-  T c = R[2] * v[0] + R[5] * v[1] + R[8] * v[2];
+template <class T> inline void mulRv(T* r, const T* R, const T* v) { tfn::mulRv(r, R, v, 3); }   // dMultiply0_331
+template <class T> inline void mulRtv(T* r, const T* R, const T* v) { tfn::mulRtv(r, R, v, 3); } // dMultiply1_331
+// symmetric 3x3 (xx xy xz yy yz zz) times vector
+template <class T> inline void symMulV(T* r, const T* S, const T* v) {
+  T a = tfn::dot3(S[0], S[1], S[2], v[0], v[1], v[2]);
+  T b = tfn::dot3(S[1], S[3], S[4], v[0], v[1], v[2]);
+  T c = tfn::dot3(S[2], S[4], S[5], v[0], v[1], v[2]);
   r[0] = a; r[1] = b; r[2] = c;
 }
 template <class T> inline bool normalize3(T* a) {
@@ -287,7 +284,7 @@ template <class T> struct World {
     else QMul3(qerr, body[j.b1].q, j.qrel);
     T cost2 = qerr[0];
     T sint2 = std::sqrt(qerr[1] * qerr[1] + qerr[2] * qerr[2] + qerr[3] * qerr[3]);
-    T theta = (dot3(qerr + 1, j.axis1) >= 0) ? (2 * std::atan2(sint2, cost2)) : (2 * std::atan2(sint2, -cost2));
+    T theta = (dot3(qerr + 1, j.axis1) >= 0) ? (2 * tfn::atan2(sint2, cost2)) : (2 * tfn::atan2(sint2, -cost2));
     if (theta > T(M_PI)) theta -= T(2 * M_PI);
     theta = -theta;
     return theta;
@@ -540,28 +537,36 @@ template <class T> struct World {
     contact.clear();  // dJointGroupEmpty
   }
 
+  // One island of dWorldQuickStep.  Arithmetic layout (the algebra is ODE's quickstep.cpp; the grouping of the
+  // floating-point operations is this engine's numerics contract, shared with the CUDA kernel):
+  //   invI_w  symmetric, 6 entries  S(r,c) = fma(R[r][2], i2*R[c][2], fma(R[r][1], i1*R[c][1], R[r][0]*(i0*R[c][0])))
+  //   gyro    tau -= w x (R (Ib .* (R^T w)))
+  //   rhs_i   = fma(c_i, 1/h, -(dot6(J1,t1) + dot6(J2,t2))),  t = f/m + v/h | invI tau + w/h
+  //   Ad_i    = sor_w / (d1 + d2 + cfm_i/h),  d = fma(1/m, dot3(Jl,Jl), dot3(invI Ja, Ja))
+  //   sweep   delta = fma(Ad, rhs - (dot6(J1,fc1) + dot6(J2,fc2)), -(lambda * (Ad*cfm/h)));  clamp;
+  //           fc_lin = fma(delta/m, Jl, fc_lin);  fc_ang = fma(delta, invI Ja, fc_ang)
+  // ODE pre-scales J and rhs by Ad and stores iMJ = M^-1 J^T; the form above is algebraically the same
+  // update with J kept unscaled (half the per-row storage on the GPU).
   void stepIsland(const std::vector<int>& ib, const std::vector<Joint<T>*>& ij, T h) {
     const int nb = (int)ib.size();
     const T fps = T(1) / h;
     std::vector<int> local(body.size(), -1);
     for (int i = 0; i < nb; i++) local[ib[i]] = i;
-    // world-frame inverse inertia, gyroscopic torque, gravity
-    std::vector<T> invI((size_t)nb * 9);
+    std::vector<T> invI((size_t)nb * 6);
     for (int i = 0; i < nb; i++) {
       Body<T>& b = body[ib[i]];
-      T* iI = &invI[(size_t)i * 9];
-      // invI = R * diag(invI_b) * R^T ; I = R * diag(I_b) * R^T
-      T Iw[9];
-      for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) {
-        T s = 0, s2 = 0;
-        for (int k = 0; k < 3; k++) { s += b.R[r * 3 + k] * (b.invI[k] * b.R[c * 3 + k]); s2 += b.R[r * 3 + k] * (b.I[k] * b.R[c * 3 + k]); }
-        iI[r * 3 + c] = s; Iw[r * 3 + c] = s2;
-      }
-      T tmp[3]; mulRv(tmp, Iw, b.avel);
-      T cr[3]; cross3(cr, b.avel, tmp);
+      T* S = &invI[(size_t)i * 6];
+      const T* R = b.R;
+      int n = 0;
+      for (int r = 0; r < 3; r++) for (int c = r; c < 3; c++)
+        S[n++] = tfn::fma(R[r * 3 + 2], b.invI[2] * R[c * 3 + 2], tfn::fma(R[r * 3 + 1], b.invI[1] * R[c * 3 + 1], R[r * 3 + 0] * (b.invI[0] * R[c * 3 + 0])));
+      T wl[3]; mulRtv(wl, R, b.avel);
+      wl[0] *= b.I[0]; wl[1] *= b.I[1]; wl[2] *= b.I[2];
+      T Iw[3]; mulRv(Iw, R, wl);
+      T cr[3]; cross3(cr, b.avel, Iw);
       for (int k = 0; k < 3; k++) b.tacc[k] -= cr[k];  // gyroscopic mode on (dBodyCreate default)
+      for (int k = 0; k < 3; k++) b.facc[k] += b.mass * gravity[k];
     }
-    for (int i = 0; i < nb; i++) { Body<T>& b = body[ib[i]]; for (int k = 0; k < 3; k++) b.facc[k] += b.mass * gravity[k]; }
     // rows
     Rows rw;
     for (Joint<T>* jp : ij) {
@@ -574,23 +579,20 @@ template <class T> struct World {
     last_rows += m;
     std::vector<T> cforce((size_t)nb * 6, T(0));
     if (m > 0) {
-      // jb -> island-local body indices
       for (int i = 0; i < m; i++) { rw.jb[i * 2] = local[rw.jb[i * 2]]; if (rw.jb[i * 2 + 1] >= 0) rw.jb[i * 2 + 1] = local[rw.jb[i * 2 + 1]]; }
-      // rhs = c/h - J*(v/h + invM*fe) ; cfm *= 1/h
       std::vector<T> tmp1((size_t)nb * 6), rhs(m);
       for (int i = 0; i < nb; i++) {
         Body<T>& b = body[ib[i]];
         for (int k = 0; k < 3; k++) tmp1[i * 6 + k] = b.facc[k] * b.invMass + b.lvel[k] * fps;
-        T t[3]; mulRv(t, &invI[(size_t)i * 9], b.tacc);
+        T t[3]; symMulV(t, &invI[(size_t)i * 6], b.tacc);
         for (int k = 0; k < 3; k++) tmp1[i * 6 + 3 + k] = t[k] + b.avel[k] * fps;
       }
       for (int i = 0; i < m; i++) {
         const T* Jr = &rw.J[(size_t)i * 12];
         int b1 = rw.jb[i * 2], b2 = rw.jb[i * 2 + 1];
-        T s = 0;
-        for (int k = 0; k < 6; k++) s += Jr[k] * tmp1[b1 * 6 + k];
-        if (b2 >= 0) for (int k = 0; k < 6; k++) s += Jr[6 + k] * tmp1[b2 * 6 + k];
-        rhs[i] = rw.c[i] * fps - s;
+        T s = tfn::dot6(Jr, &tmp1[(size_t)b1 * 6]);
+        if (b2 >= 0) s = s + tfn::dot6(Jr + 6, &tmp1[(size_t)b2 * 6]);
+        rhs[i] = tfn::fma(rw.c[i], fps, -s);
         rw.cfm[i] *= fps;
       }
       std::vector<T> lambda(m, T(0));
@@ -600,13 +602,10 @@ template <class T> struct World {
     for (int i = 0; i < nb; i++) {
       Body<T>& b = body[ib[i]];
       for (int k = 0; k < 3; k++) { b.lvel[k] += h * cforce[i * 6 + k]; b.avel[k] += h * cforce[i * 6 + 3 + k]; }
-    }
-    for (int i = 0; i < nb; i++) {
-      Body<T>& b = body[ib[i]];
       T hm = h * b.invMass;
       T ht[3];
       for (int k = 0; k < 3; k++) { b.lvel[k] += hm * b.facc[k]; ht[k] = b.tacc[k] * h; }
-      T t[3]; mulRv(t, &invI[(size_t)i * 9], ht);
+      T t[3]; symMulV(t, &invI[(size_t)i * 6], ht);
       for (int k = 0; k < 3; k++) b.avel[k] += t[k];
     }
   }
@@ -615,32 +614,19 @@ template <class T> struct World {
   void sorLcp(int m, int nb, Rows& rw, const std::vector<T>& invI, const std::vector<int>& ib,
               std::vector<T>& lambda, std::vector<T>& fc, std::vector<T>& b) {
     (void)nb;
-    std::vector<T> iMJ((size_t)m * 12, T(0)), Ad(m);
+    std::vector<T> Ad(m), Adcfm(m);
     for (int i = 0; i < m; i++) {
-      const T* Jr = &rw.J[(size_t)i * 12]; T* iM = &iMJ[(size_t)i * 12];
+      const T* Jr = &rw.J[(size_t)i * 12];
       int b1 = rw.jb[i * 2], b2 = rw.jb[i * 2 + 1];
-      T k = body[ib[b1]].invMass;
-      for (int c = 0; c < 3; c++) iM[c] = k * Jr[c];
-      mulRv(iM + 3, &invI[(size_t)b1 * 9], Jr + 3);
+      T a[3]; symMulV(a, &invI[(size_t)b1 * 6], Jr + 3);
+      T diag = tfn::fma(body[ib[b1]].invMass, dot3(Jr, Jr), dot3(a, Jr + 3));
       if (b2 >= 0) {
-        k = body[ib[b2]].invMass;
-        for (int c = 0; c < 3; c++) iM[6 + c] = k * Jr[6 + c];
-        mulRv(iM + 9, &invI[(size_t)b2 * 9], Jr + 9);
+        symMulV(a, &invI[(size_t)b2 * 6], Jr + 9);
+        diag = diag + tfn::fma(body[ib[b2]].invMass, dot3(Jr + 6, Jr + 6), dot3(a, Jr + 9));
       }
+      Ad[i] = sor_w / (diag + rw.cfm[i]);
+      Adcfm[i] = Ad[i] * rw.cfm[i];
     }
-    for (int i = 0; i < m; i++) {
-      const T* Jr = &rw.J[(size_t)i * 12]; const T* iM = &iMJ[(size_t)i * 12];
-      T sum = 0;
-      for (int c = 0; c < 6; c++) sum += iM[c] * Jr[c];
-      if (rw.jb[i * 2 + 1] >= 0) for (int c = 6; c < 12; c++) sum += iM[c] * Jr[c];
-      Ad[i] = sor_w / (sum + rw.cfm[i]);
-    }
-    for (int i = 0; i < m; i++) {
-      T* Jr = &rw.J[(size_t)i * 12];
-      for (int c = 0; c < 12; c++) Jr[c] *= Ad[i];
-      b[i] *= Ad[i];
-    }
-    for (int i = 0; i < m; i++) Ad[i] *= rw.cfm[i];
     std::vector<int> order(m);
     { int j = 0, k = 1;
       for (int i = 0; i < m; i++) { if (rw.findex[i] < 0) order[j++] = i; else { order[m - k] = i; k++; } } }
@@ -656,21 +642,25 @@ template <class T> struct World {
         int b1 = rw.jb[idx * 2], b2 = rw.jb[idx * 2 + 1];
         const T* Jr = &rw.J[(size_t)idx * 12];
         T old = lambda[idx];
-        T delta = b[idx] - old * Ad[idx];
         T* f1 = &fc[(size_t)b1 * 6];
-        delta -= f1[0] * Jr[0] + f1[1] * Jr[1] + f1[2] * Jr[2] + f1[3] * Jr[3] + f1[4] * Jr[4] + f1[5] * Jr[5];
-        T* f2 = nullptr;
-        if (b2 >= 0) {
-          f2 = &fc[(size_t)b2 * 6];
-          delta -= f2[0] * Jr[6] + f2[1] * Jr[7] + f2[2] * Jr[8] + f2[3] * Jr[9] + f2[4] * Jr[10] + f2[5] * Jr[11];
-        }
+        T* f2 = b2 >= 0 ? &fc[(size_t)b2 * 6] : nullptr;
+        T sum = tfn::dot6(Jr, f1);
+        if (f2) sum = sum + tfn::dot6(Jr + 6, f2);
+        T delta = tfn::fma(Ad[idx], b[idx] - sum, -(old * Adcfm[idx]));
         T nl = old + delta;
         if (nl < lo_act) { delta = lo_act - old; lambda[idx] = lo_act; }
         else if (nl > hi_act) { delta = hi_act - old; lambda[idx] = hi_act; }
         else lambda[idx] = nl;
-        const T* iM = &iMJ[(size_t)idx * 12];
-        for (int c = 0; c < 6; c++) f1[c] += delta * iM[c];
-        if (f2) for (int c = 0; c < 6; c++) f2[c] += delta * iM[6 + c];
+        {
+          const T dm = delta * body[ib[b1]].invMass;
+          T a[3]; symMulV(a, &invI[(size_t)b1 * 6], Jr + 3);
+          for (int c = 0; c < 3; c++) { f1[c] = tfn::fma(dm, Jr[c], f1[c]); f1[3 + c] = tfn::fma(delta, a[c], f1[3 + c]); }
+        }
+        if (f2) {
+          const T dm = delta * body[ib[b2]].invMass;
+          T a[3]; symMulV(a, &invI[(size_t)b2 * 6], Jr + 9);
+          for (int c = 0; c < 3; c++) { f2[c] = tfn::fma(dm, Jr[6 + c], f2[c]); f2[3 + c] = tfn::fma(delta, a[c], f2[3 + c]); }
+        }
       }
     }
   }

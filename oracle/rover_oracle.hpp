@@ -86,9 +86,10 @@ struct Policy {
   void infer(const float* x, float* y) const {
     const int H = TFODE_MLP_HIDDEN;
     std::vector<float> h1(H), h2(H);
-    for (int j = 0; j < H; j++) { float s = b1[j]; for (int i = 0; i < 17; i++) s += x[i] * W1[i * H + j]; h1[j] = s > 0 ? s : 0; }
-    for (int j = 0; j < H; j++) { float s = b2[j]; for (int i = 0; i < H; i++) s += h1[i] * W2[i * H + j]; h2[j] = s > 0 ? s : 0; }
-    for (int j = 0; j < 2; j++) { float s = b3[j]; for (int i = 0; i < H; i++) s += h2[i] * W3[i * 2 + j]; y[j] = std::tanh(s); }
+    // fp32 with one fma per weight, accumulated in input order starting from the bias (numerics contract)
+    for (int j = 0; j < H; j++) { float s = b1[j]; for (int i = 0; i < 17; i++) s = tfn::fma(x[i], W1[i * H + j], s); h1[j] = s > 0 ? s : 0; }
+    for (int j = 0; j < H; j++) { float s = b2[j]; for (int i = 0; i < H; i++) s = tfn::fma(h1[i], W2[i * H + j], s); h2[j] = s > 0 ? s : 0; }
+    for (int j = 0; j < 2; j++) { float s = b3[j]; for (int i = 0; i < H; i++) s = tfn::fma(h2[i], W3[i * 2 + j], s); y[j] = tfn::tanh(s); }
   }
 };
 
@@ -276,7 +277,11 @@ template <class T> struct RoverSim {
       b.pos[0] = s == 0 ? 1 : 2; b.pos[1] = 0; b.pos[2] = step_height / 2;
       double l = s == 0 ? 1 : 2;
       b.setMassBoxTotal(1, l, 3, step_height);
-      if (s == 0) { double Rs[9]; RFromEulerAngles(Rs, 0.0, 0.0, step_yaw_deg * M_PI / 180); b.setRotation(Rs); }
+      if (s == 0) {  // dRFromEulerAngles(0,0,psi) with the contract's sin/cos (the yaw is re-drawn on the device at every auto-reset)
+        double sp, cp; tfn::d_sincos(step_yaw_deg * 3.14159265358979323846 / 180.0, &sp, &cp);
+        double Rs[9] = {cp, sp, 0, -sp, cp, 0, 0, 0, 1};
+        b.setRotation(Rs);
+      }
       wd.body.push_back(b);
       step_side[s][0] = (T)l; step_side[s][1] = 3; step_side[s][2] = (T)step_height;
       int bi = (int)wd.body.size() - 1;
@@ -323,13 +328,13 @@ template <class T> struct RoverSim {
   }
   T getDirection() const {
     T v[3], e[3] = {1, 0, 0}; w.body[0].vectorToWorld(e, v);
-    T direction = std::asin(v[1]) * (T)RAD_TO_DEG;
+    T direction = tfn::asin(v[1]) * (T)RAD_TO_DEG;
     if (v[0] < 0) direction = (v[1] > 0 ? 1 : -1) * T(180) - direction;
     return direction;
   }
   bool isUpsideDown() const { T v[3], e[3] = {0, 0, 1}; w.body[0].vectorToWorld(e, v); return v[2] < 0; }
-  T getRollAngle() const { T v[3], e[3] = {0, 1, 0}; w.body[0].vectorToWorld(e, v); return std::asin(v[2]) * (T)RAD_TO_DEG; }
-  T getPitchAngle() const { T v[3], e[3] = {1, 0, 0}; w.body[0].vectorToWorld(e, v); return std::asin(-v[2]) * (T)RAD_TO_DEG; }
+  T getRollAngle() const { T v[3], e[3] = {0, 1, 0}; w.body[0].vectorToWorld(e, v); return tfn::asin(v[2]) * (T)RAD_TO_DEG; }
+  T getPitchAngle() const { T v[3], e[3] = {1, 0, 0}; w.body[0].vectorToWorld(e, v); return tfn::asin(-v[2]) * (T)RAD_TO_DEG; }
   T getBoggieAngle() const { return w.hingeAngle(w.joint[j_boggie]) * (T)RAD_TO_DEG; }
   T getSteeringTrueAngle() const { return w.hingeAngle(w.joint[j_servo]) * (T)RAD_TO_DEG; }
   void getState(double* s) const {  // Rover_1_tf::GetState, src/rover_1_tf.cc:60-77
@@ -346,7 +351,7 @@ template <class T> struct RoverSim {
   void geomPose(const Geom<T>& g, T* p, T* R) const {
     const Body<T>& b = w.body[g.body];
     b.relPointPos(g.off, p);
-    if (g.has_rot) { for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) { T s = 0; for (int k = 0; k < 3; k++) s += b.R[r * 3 + k] * g.offR[k * 3 + c]; R[r * 3 + c] = s; } }
+    if (g.has_rot) { for (int r = 0; r < 3; r++) for (int c = 0; c < 3; c++) R[r * 3 + c] = tfn::dot3(b.R[r * 3], b.R[r * 3 + 1], b.R[r * 3 + 2], g.offR[c], g.offR[3 + c], g.offR[6 + c]); }
     else for (int k = 0; k < 9; k++) R[k] = b.R[k];
   }
   void cylAABB(const T* p, const T* R, T radius, T lz, T* lo, T* hi) const {  // dxCylinder::computeAABB
@@ -473,7 +478,7 @@ template <class T> struct RoverSim {
     T n = std::sqrt(qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
     T angle, axis[3];
     if (n != T(0)) {
-      angle = T(2) * std::atan2(n, std::fabs(qr[0]));
+      angle = T(2) * tfn::atan2(n, std::fabs(qr[0]));
       if (qr[0] < T(0)) n = -n;
       axis[0] = qr[1] / n; axis[1] = qr[2] / n; axis[2] = qr[3] / n;
     } else { angle = 0; axis[0] = 1; axis[1] = 0; axis[2] = 0; }
@@ -509,8 +514,8 @@ template <class T> struct RoverSim {
     T diff[4], trans[4], min_speed = 0, adjusted_speed;
     const T wb = (T)wheelbase, wt = (T)wheeltrack, rs = (T)robot_speed;
     for (int i = 0; i < 4; i++) {
-      diff[i] = (i % 2 ? -1 : 1) * wt / wb * std::tan(gamma / 2);
-      trans[i] = (i / 2 ? -1 : 1) * (-wb * std::tan(gamma / 2) + (i % 2 ? -1 : 1) * wt) * dgamma_dt / 4;
+      diff[i] = (i % 2 ? -1 : 1) * wt / wb * tfn::tan(gamma / 2);
+      trans[i] = (i / 2 ? -1 : 1) * (-wb * tfn::tan(gamma / 2) + (i % 2 ? -1 : 1) * wt) * dgamma_dt / 4;
       if (crawling_mode) {
         if (rs >= 0) min_speed = std::max(min_speed, -trans[i] / (1 + diff[i]));
         else min_speed = std::min(min_speed, -trans[i] / (1 + diff[i]));

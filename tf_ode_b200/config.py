@@ -52,7 +52,7 @@ def make_config(preset, n_envs=1, **kw):
     c.hf_length = c.hf_width = 3.0
     c.hf_pos[0] = c.hf_pos[1] = c.hf_pos[2] = 0.0
     c.seed = 20260411
-    c.max_contacts = 32
+    c.max_contacts = 24
     c.transition_capacity = 0
     if preset == abi.PRESET_SCENE_1:
         pass

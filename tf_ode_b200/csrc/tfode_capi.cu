@@ -51,94 +51,159 @@ struct TfodeBatch {
 // ode/box.hh:54-62, ode/ft_sensor.cc:50-55 and the step boxes of src/rover_training_1.cc:88-98).
 // ------------------------------------------------------------------------------------------------
 namespace {
-struct BodySpec { double x, y, z, mass, lx, ly, lz; int cyl; };  // cyl: dMassSetCylinderTotal(axis z, r=lx, l=lz)
+// A miniature of the construction calls the reference makes (dBodySetPosition/Rotation, dMassSet*Total,
+// dJointSetHingeAnchor/Axis, dJointSetSliderAxis, dGeomSetOffsetWorldPosition), evaluated in double like libode
+// and rounded to float once, when the tables are written.
+struct DBody { double pos[3], q[4], R[9], mass, I[3]; };
+
+void d_RFromEuler(double* R, double phi, double theta, double psi) {  // dRFromEulerAngles
+  double sphi = std::sin(phi), cphi = std::cos(phi), sth = std::sin(theta), cth = std::cos(theta), spsi = std::sin(psi), cpsi = std::cos(psi);
+  R[0] = cpsi * cth; R[1] = spsi * cth; R[2] = -sth;
+  R[3] = cpsi * sth * sphi - spsi * cphi; R[4] = spsi * sth * sphi + cpsi * cphi; R[5] = cth * sphi;
+  R[6] = cpsi * sth * cphi + spsi * sphi; R[7] = spsi * sth * cphi - cpsi * sphi; R[8] = cth * cphi;
+}
+void d_QfromR(double* q, const double* R) {  // dRtoQ, tr >= 0 branch is the only one the rover's construction reaches
+  double tr = R[0] + R[4] + R[8];
+  double s = std::sqrt(tr + 1); q[0] = 0.5 * s; s = 0.5 / s;
+  q[1] = (R[7] - R[5]) * s; q[2] = (R[2] - R[6]) * s; q[3] = (R[3] - R[1]) * s;
+}
+void d_RfromQ(double* R, const double* q) {
+  double qq1 = 2 * q[1] * q[1], qq2 = 2 * q[2] * q[2], qq3 = 2 * q[3] * q[3];
+  R[0] = 1 - qq2 - qq3; R[1] = 2 * (q[1] * q[2] - q[0] * q[3]); R[2] = 2 * (q[1] * q[3] + q[0] * q[2]);
+  R[3] = 2 * (q[1] * q[2] + q[0] * q[3]); R[4] = 1 - qq1 - qq3; R[5] = 2 * (q[2] * q[3] - q[0] * q[1]);
+  R[6] = 2 * (q[1] * q[3] - q[0] * q[2]); R[7] = 2 * (q[2] * q[3] + q[0] * q[1]); R[8] = 1 - qq1 - qq2;
+}
+void d_setRotation(DBody& b, const double* Rin) {  // dBodySetRotation: R -> q -> normalise -> R
+  d_QfromR(b.q, Rin);
+  double l = b.q[0] * b.q[0] + b.q[1] * b.q[1] + b.q[2] * b.q[2] + b.q[3] * b.q[3];
+  l = 1.0 / std::sqrt(l);
+  for (int k = 0; k < 4; k++) b.q[k] *= l;
+  d_RfromQ(b.R, b.q);
+}
+DBody d_body(double x, double y, double z) {
+  DBody b; b.pos[0] = x; b.pos[1] = y; b.pos[2] = z; b.q[0] = 1; b.q[1] = b.q[2] = b.q[3] = 0;
+  for (int k = 0; k < 9; k++) b.R[k] = (k % 4 == 0) ? 1.0 : 0.0;
+  b.mass = 1; b.I[0] = b.I[1] = b.I[2] = 1; return b;
+}
+void d_massBox(DBody& b, double m, double lx, double ly, double lz) {  // dMassSetBoxTotal
+  b.mass = m; b.I[0] = m / 12.0 * (ly * ly + lz * lz); b.I[1] = m / 12.0 * (lx * lx + lz * lz); b.I[2] = m / 12.0 * (lx * lx + ly * ly);
+}
+void d_massCylZ(DBody& b, double m, double r, double l) {  // dMassSetCylinderTotal(direction 3)
+  double r2 = r * r;
+  b.mass = m; b.I[0] = b.I[1] = m * (0.25 * r2 + (1.0 / 12.0) * l * l); b.I[2] = m * 0.5 * r2;
+}
+void d_posRelPoint(const DBody& b, const double* p, double* out) {  // dBodyGetPosRelPoint
+  double d[3] = {p[0] - b.pos[0], p[1] - b.pos[1], p[2] - b.pos[2]};
+  tfn::mulRtv(out, b.R, d, 3);
+}
+void d_qmulInvA(double* r, const double* b, const double* c) {  // b^-1 * c
+  r[0] = b[0] * c[0] + b[1] * c[1] + b[2] * c[2] + b[3] * c[3];
+  r[1] = b[0] * c[1] - b[1] * c[0] - b[2] * c[3] + b[3] * c[2];
+  r[2] = b[0] * c[2] - b[2] * c[0] - b[3] * c[1] + b[1] * c[3];
+  r[3] = b[0] * c[3] - b[3] * c[0] - b[1] * c[2] + b[2] * c[1];
+}
 
 void build_model(Model& M) {
   std::memset(&M, 0, sizeof(M));
+  // parameters of src/rover_1.cc:49-103
   const double wheelbase = 0.58, wheeltrack = 0.61, wheel_r = 0.105, wheel_w = 0.1, belly = 0.33;
   const double front_len = 0.345, front_h = 0.225, front_w = 0.200;
-  const double fx = front_len / 2 - 0.063, fy = 0.023, fz = belly + front_h / 2;
+  const double fx = front_len / 2 + -0.063, fy = 0.023, fz = belly + front_h / 2;
   const double rear_len = 0.312, rear_h = 0.177, rear_w = 0.126;
   const double rx = -rear_len / 2 + 0.046, ry = -0.040, rz = belly + rear_h / 2;
   const double sea_elev = belly + 0.12;
   const double boggie_h = sea_elev - belly;
   const double fork_elev = belly - 0.1 / 2;
   const double rim_r = wheel_r - wheel_w / 2;
-  const float step_h = (float)(0.105 * 2);
-  const BodySpec bs[NB] = {
-      {fx, fy, fz, 5.25, front_len, front_w, front_h, 0},
-      {0.285, 0, belly + 0.155, 3, 0.0975, 0.151, 0.065, 0},
-      {rx, ry, rz, 3.67, rear_len, rear_w, rear_h, 0},
-      {-wheelbase / 2 + 0.035, 0, belly + boggie_h / 2, 1, 0.1, 0.1, boggie_h, 0},
-      {wheelbase / 2, 0, fork_elev, 1, 0.05, 0.3, 0.1, 0},
-      {-wheelbase / 2, 0, fork_elev, 1, 0.05, 0.3, 0.1, 0},
-      {wheelbase / 2, wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
-      {wheelbase / 2, -wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
-      {-wheelbase / 2, wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
-      {-wheelbase / 2, -wheeltrack / 2, wheel_r, 2.4, rim_r, 0, wheel_w, 1},
-      {1, 0, step_h / 2, 1, 1, 3, step_h, 0},
-      {2, 0, step_h / 2, 1, 2, 3, step_h, 0}};
-  const double s2 = std::sqrt(0.5);
+  const float step_h = (float)(0.105 * 2);  // `float step_height` in src/rover_training_1.cc:84
+  DBody B[NB];
+  B[0] = d_body(fx, fy, fz); d_massBox(B[0], 5.25, front_len, front_w, front_h);
+  B[1] = d_body(0.285, 0, belly + 0.155); d_massBox(B[1], 3, 0.0975, 0.151, 0.065);
+  B[2] = d_body(rx, ry, rz); d_massBox(B[2], 3.67, rear_len, rear_w, rear_h);
+  B[3] = d_body(-wheelbase / 2 + 0.035, 0, belly + boggie_h / 2); d_massBox(B[3], 1, 0.1, 0.1, boggie_h);
+  B[4] = d_body(wheelbase / 2, 0, fork_elev); d_massBox(B[4], 1, 0.05, 0.3, 0.1);
+  B[5] = d_body(-wheelbase / 2, 0, fork_elev); d_massBox(B[5], 1, 0.05, 0.3, 0.1);
+  double Rw[9]; d_RFromEuler(Rw, M_PI / 2, 0.0, 0.0);  // src/rover_1.cc:214
+  for (int i = 0; i < 4; i++) {
+    B[6 + i] = d_body((i / 2 ? -1 : 1) * wheelbase / 2, (i % 2 ? -1 : 1) * wheeltrack / 2, wheel_r);
+    d_massCylZ(B[6 + i], 1.4 + 1, rim_r, wheel_w);
+    d_setRotation(B[6 + i], Rw);
+  }
+  B[10] = d_body(1, 0, step_h / 2); d_massBox(B[10], 1, 1, 3, step_h);   // yaw is per episode (reset_env)
+  B[11] = d_body(2, 0, step_h / 2); d_massBox(B[11], 1, 2, 3, step_h);
   for (int b = 0; b < NB; b++) {
-    const BodySpec& s = bs[b];
-    double I[3];
-    if (s.cyl) { double r2 = s.lx * s.lx; I[0] = I[1] = s.mass * (0.25 * r2 + s.lz * s.lz / 12.0); I[2] = s.mass * 0.5 * r2; }
-    else { I[0] = s.mass / 12.0 * (s.ly * s.ly + s.lz * s.lz); I[1] = s.mass / 12.0 * (s.lx * s.lx + s.lz * s.lz); I[2] = s.mass / 12.0 * (s.lx * s.lx + s.ly * s.ly); }
-    M.mass[b] = (float)s.mass; M.invMass[b] = (float)(1.0 / s.mass);
-    for (int k = 0; k < 3; k++) { M.Ib[b][k] = (float)I[k]; M.invIb[b][k] = (float)(1.0 / I[k]); }
-    M.pos0[b][0] = (float)s.x; M.pos0[b][1] = (float)s.y; M.pos0[b][2] = (float)s.z;
-    // wheels: dRFromEulerAngles(pi/2,0,0) = rows (1,0,0),(0,0,1),(0,-1,0) -> quaternion (sqrt(1/2), -sqrt(1/2), 0, 0)
-    M.quat0[b][0] = s.cyl ? (float)s2 : 1.0f; M.quat0[b][1] = s.cyl ? (float)-s2 : 0.0f;
+    M.mass[b] = (float)B[b].mass; M.invMass[b] = (float)(1.0 / B[b].mass);
+    for (int k = 0; k < 3; k++) { M.Ib[b][k] = (float)B[b].I[k]; M.invIb[b][k] = (float)(1.0 / B[b].I[k]); M.pos0[b][k] = (float)B[b].pos[k]; }
+    for (int k = 0; k < 4; k++) M.quat0[b][k] = (float)B[b].q[k];
   }
   M.step_side[0][0] = 1; M.step_side[0][1] = 3; M.step_side[0][2] = step_h;
   M.step_side[1][0] = 2; M.step_side[1][1] = 3; M.step_side[1][2] = step_h;
-  // joints: body frames are the world frame for every rover body except the wheels (R_w^T v = (v.x, -v.z, v.y))
-  auto P = [&](int b, int k) { return k == 0 ? bs[b].x : (k == 1 ? bs[b].y : bs[b].z); };
-  auto set_hinge = [&](int j, int b1, int b2, const double* anchor, const double* axis, bool b2_is_wheel) {
+
+  auto set_axes = [&](int j, int b1, int b2, double x, double y, double z) {  // setAxes (joint.cpp)
+    double a[3] = {x, y, z}; double l = tfn::dot3(a, a); l = 1.0 / std::sqrt(l); a[0] *= l; a[1] *= l; a[2] *= l;
+    double o[3];
+    tfn::mulRtv(o, B[b1].R, a, 3); for (int k = 0; k < 3; k++) M.axis1[j][k] = (float)o[k];
+    if (b2 < NB) { tfn::mulRtv(o, B[b2].R, a, 3); for (int k = 0; k < 3; k++) M.axis2[j][k] = (float)o[k]; }
+    else for (int k = 0; k < 3; k++) M.axis2[j][k] = (float)a[k];
+  };
+  auto set_qrel = [&](int j, int b1, int b2) {  // computeInitialRelativeRotation
+    double q[4];
+    if (b2 < NB) d_qmulInvA(q, B[b1].q, B[b2].q); else { q[0] = B[b1].q[0]; for (int k = 1; k < 4; k++) q[k] = -B[b1].q[k]; }
+    for (int k = 0; k < 4; k++) M.qrel[j][k] = (float)q[k];
+  };
+  auto hinge = [&](int j, int b1, int b2, const double* anchor, double ax, double ay, double az) {
     M.jb1[j] = b1; M.jb2[j] = b2; M.jslider[j] = 0;
-    for (int k = 0; k < 3; k++) { M.anchor1[j][k] = (float)(anchor[k] - P(b1, k)); M.axis1[j][k] = (float)axis[k]; }
-    double d[3] = {anchor[0] - P(b2, 0), anchor[1] - P(b2, 1), anchor[2] - P(b2, 2)};
-    if (b2_is_wheel) {
-      M.anchor2[j][0] = (float)d[0]; M.anchor2[j][1] = (float)-d[2]; M.anchor2[j][2] = (float)d[1];
-      M.axis2[j][0] = (float)axis[0]; M.axis2[j][1] = (float)-axis[2]; M.axis2[j][2] = (float)axis[1];
-      M.qrel[j][0] = (float)s2; M.qrel[j][1] = (float)-s2;
-    } else {
-      for (int k = 0; k < 3; k++) { M.anchor2[j][k] = (float)d[k]; M.axis2[j][k] = (float)axis[k]; }
-      M.qrel[j][0] = 1;
-    }
+    double o[3];
+    d_posRelPoint(B[b1], anchor, o); for (int k = 0; k < 3; k++) M.anchor1[j][k] = (float)o[k];
+    d_posRelPoint(B[b2], anchor, o); for (int k = 0; k < 3; k++) M.anchor2[j][k] = (float)o[k];
+    set_axes(j, b1, b2, ax, ay, az);
+    set_qrel(j, b1, b2);
     M.lostop[j] = -INFINITY; M.histop[j] = INFINITY;
   };
-  // 0: battery clamp slider (battery, main), axis y, lo = hi = 0
-  M.jb1[0] = 1; M.jb2[0] = 0; M.jslider[0] = 1; M.axis1[0][1] = 1; M.qrel[0][0] = 1;
-  for (int k = 0; k < 3; k++) M.offset[0][k] = (float)(P(1, k) - P(0, k));
-  { const double a[3] = {0, 0, (fz + rz) / 2}, ax[3] = {0, 0, 1}; set_hinge(1, 2, 0, a, ax, false); }  // centre hinge servo
-  { const double a[3] = {-wheelbase / 2, 0, sea_elev}, ax[3] = {1, 0, 0}; set_hinge(2, 3, 2, a, ax, false);  // boggie hinge, stops +-45 deg
+  auto slider = [&](int j, int b1, int b2, double ax, double ay, double az) {
+    M.jb1[j] = b1; M.jb2[j] = b2; M.jslider[j] = 1;
+    set_axes(j, b1, b2, ax, ay, az);
+    if (b2 < NB) {  // computeOffset
+      double c[3] = {B[b1].pos[0] - B[b2].pos[0], B[b1].pos[1] - B[b2].pos[1], B[b1].pos[2] - B[b2].pos[2]}, o[3];
+      tfn::mulRtv(o, B[b2].R, c, 3);
+      for (int k = 0; k < 3; k++) M.offset[j][k] = (float)o[k];
+    } else for (int k = 0; k < 3; k++) M.offset[j][k] = (float)B[b1].pos[k];
+    set_qrel(j, b1, b2);
+    M.lostop[j] = 0; M.histop[j] = 0;
+  };
+  slider(0, 1, 0, 0, 1, 0);                                                    // battery clamp, src/rover_1.cc:128-132
+  { const double a[3] = {0, 0, (fz + rz) / 2}; hinge(1, 2, 0, a, 0, 0, 1); }   // centre hinge servo, :181-189
+  { const double a[3] = {-wheelbase / 2, 0, sea_elev}; hinge(2, 3, 2, a, 1, 0, 0);  // boggie hinge, :194-200
     M.lostop[2] = (float)(-45 * 0.017453292519943295); M.histop[2] = (float)(45 * 0.017453292519943295); }
-  for (int i = 0; i < 4; i++) {
-    const double a[3] = {P(6 + i, 0), P(6 + i, 1), P(6 + i, 2)}, ax[3] = {0, -1, 0};
-    set_hinge(3 + i, P(6 + i, 0) > 0 ? 4 : 5, 6 + i, a, ax, true);
-  }
-  for (int s = 0; s < 2; s++) { M.jb1[7 + s] = 10 + s; M.jb2[7 + s] = 15; M.jslider[7 + s] = 1; M.axis1[7 + s][2] = 1; }  // Object::fix
-  // geoms
-  for (int k = 0; k < 50; k++) { M.ring[k][0] = (float)(rim_r * std::cos(k * 2 * M_PI / 50)); M.ring[k][1] = (float)(rim_r * std::sin(k * 2 * M_PI / 50)); }
+  for (int i = 0; i < 4; i++) hinge(3 + i, B[6 + i].pos[0] > 0 ? 4 : 5, 6 + i, B[6 + i].pos, 0, -1, 0);  // wheel hinges, :224-229
+  slider(7, 10, 15, 0, 0, 1); slider(8, 11, 15, 0, 0, 1);                      // Object::fix, ode/object.cc:155-179
+
+  // geoms (ode/wheel.hh:63-73, src/rover_1.cc:116-176)
+  for (int k = 0; k < 50; k++) { M.ring[k][0] = (float)(rim_r * std::cos(k * 2 * M_PI / 50)); M.ring[k][1] = (float)(rim_r * std::sin(k * 2 * M_PI / 50)); M.ring[k][2] = 0; }
   M.sphere_r = (float)(wheel_w / 2);
-  for (int g = 0; g < 3; g++) { M.ns_type[g] = 1; M.ns_body[g] = g; M.ns_dim[g][0] = (float)bs[g].lx; M.ns_dim[g][1] = (float)bs[g].ly; M.ns_dim[g][2] = (float)bs[g].lz; }
+  const double chassis[3][3] = {{front_len, front_w, front_h}, {0.0975, 0.151, 0.065}, {rear_len, rear_w, rear_h}};
+  for (int g = 0; g < 3; g++) { M.ns_type[g] = 1; M.ns_body[g] = g; for (int k = 0; k < 3; k++) M.ns_dim[g][k] = (float)chassis[g][k]; }
   for (int g = 0; g < 4; g++) {  // motor bulks on the forks
-    const int body = 4 + g / 2; const double sy = (g % 2 == 0) ? 1 : -1;
+    const int body = 4 + g / 2; const double sx = g / 2 == 0 ? 1 : -1;
     M.ns_type[3 + g] = 2; M.ns_body[3 + g] = body; M.ns_rot[3 + g] = 1; M.ns_cb[3 + g] = 1;
-    M.ns_dim[3 + g][0] = 0.025f; M.ns_dim[3 + g][1] = 0.1f;
-    const double ap[3] = {bs[body].x, sy * (wheeltrack - wheel_w - 0.1) / 2, wheel_r};
-    for (int k = 0; k < 3; k++) M.ns_off[3 + g][k] = (float)(ap[k] - P(body, k));
+    M.ns_dim[3 + g][0] = (float)0.025; M.ns_dim[3 + g][1] = (float)0.1;
+    const double ap[3] = {sx * wheelbase / 2, (g % 2 == 0 ? 1 : -1) * (wheeltrack - wheel_w - 0.1) / 2, wheel_r};
+    double o[3]; d_posRelPoint(B[body], ap, o);
+    for (int k = 0; k < 3; k++) M.ns_off[3 + g][k] = (float)o[k];
+    for (int k = 0; k < 9; k++) M.ns_offR[3 + g][k] = (float)Rw[k];
   }
   for (int g = 0; g < 4; g++) { M.ns_type[7 + g] = 2; M.ns_body[7 + g] = 6 + g; M.ns_dim[7 + g][0] = (float)rim_r; M.ns_dim[7 + g][1] = (float)wheel_w; }
-  // FT sensors: centre (+-wheelbase/2, 0, belly); A = main / boggie, B = forks
+  // FT sensors (src/rover_1.cc:205-206, ode/ft_sensor.cc:50-55): A = main / boggie, B = forks
   for (int s = 0; s < 2; s++) {
     const double c[3] = {(s == 0 ? 1 : -1) * wheelbase / 2, 0, belly};
-    const int A = s == 0 ? 0 : 3, B = s == 0 ? 4 : 5;
-    for (int k = 0; k < 3; k++) { M.ft_ocA[s][k] = (float)(c[k] - P(A, k)); M.ft_ocB[s][k] = (float)(c[k] - P(B, k)); }
+    const int A = s == 0 ? 0 : 3, Bb = s == 0 ? 4 : 5;
+    double o[3];
+    d_posRelPoint(B[A], c, o); for (int k = 0; k < 3; k++) M.ft_ocA[s][k] = (float)o[k];
+    d_posRelPoint(B[Bb], c, o); for (int k = 0; k < 3; k++) M.ft_ocB[s][k] = (float)o[k];
   }
-  M.getpos_rel[0] = (float)-fx; M.getpos_rel[1] = (float)-fy; M.getpos_rel[2] = (float)(-fz + sea_elev);
-  M.robot_max_speed = (float)std::fmin(7.4351 / wheel_r, 7.4351 * wheel_r);  // Q4
+  M.getpos_rel[0] = (float)(-fx); M.getpos_rel[1] = (float)(-fy); M.getpos_rel[2] = (float)(-fz + sea_elev);
+  M.robot_max_speed = 7.4351 / wheel_r;  // Q4: divide for wheel 0, multiply for 1..3
+  for (int i = 1; i < 4; i++) M.robot_max_speed = std::fmin(M.robot_max_speed, 7.4351 * wheel_r);
   // LP_second_order_bilinear(Te = 0.001f, w0 = 4 pi, Q = 0.5f), Filters/cpp/filters.cc:148-158
   { const float Te = 0.001f; const double w0 = 4 * M_PI; const float Q = 0.5f;
     double w2T2 = std::pow(w0 * Te, 2), den = 2 * w0 * Te + 4 * Q + Q * w2T2;
@@ -161,7 +226,7 @@ int tfode_batch_config_default(TfodeBatchConfig* c, int preset) {
   c->x_goal_abs = 1; c->check_upside_down = 1; c->terminate = 0;
   c->crawler_amp = 30; c->crawler_dt_torque = 2; c->crawler_rate = 10;
   c->hf_length = 3; c->hf_width = 3;
-  c->seed = 20260411ull; c->max_contacts = 32;
+  c->seed = 20260411ull; c->max_contacts = 24;
   switch (preset) {
     case 0: break;
     case 1: c->controller = TFODE_CTRL_RANDOM; c->ic_period = 0.5f; c->ic_start = 1.0f; c->x_goal = 1.0f; c->y_max = 0.6f; c->terminate = 1; break;
@@ -193,6 +258,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   if (cfg->n_envs <= 0) { g_create_error = "n_envs must be positive"; return TFODE_EINVAL; }
   if (cfg->scene < 0 || cfg->scene > 2 || cfg->controller < 0 || cfg->controller > 3) { g_create_error = "bad scene/controller"; return TFODE_EINVAL; }
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD && (!cfg->hf_heights || cfg->hf_ncol < 2 || cfg->hf_nrow < 2)) { g_create_error = "heightfield scene without heights"; return TFODE_EINVAL; }
+  if (cfg->max_contacts < 1 || cfg->max_contacts > MAXC) { g_create_error = "max_contacts must be in 1..24"; return TFODE_EINVAL; }
   if (!(cfg->dt > 0) || cfg->pgs_iters < 1 || cfg->pgs_iters > 1000) { g_create_error = "bad dt / pgs_iters"; return TFODE_EINVAL; }
   if (std::fabs(cfg->step_yaw_deg) + std::fabs(cfg->step_yaw_jitter_deg) >= 119.0f) { g_create_error = "step yaw must stay below 119 degrees"; return TFODE_EINVAL; }
   TfodeBatch* b = new TfodeBatch();

@@ -58,6 +58,7 @@ struct __align__(16) EnvRec {
 
 // Per-GPU constants of the rover model (built on the host in double, src/rover_1.cc:49-233 restated as tables).
 struct Model {
+  double robot_max_speed;
   double filt_c[3];                   // Cy1, Cy2, Cx0 of LP_second_order_bilinear(0.001f, 4*pi, 0.5)
   float invMass[NB], mass[NB];
   float Ib[NB][3], invIb[NB][3];
@@ -65,17 +66,17 @@ struct Model {
   int jb1[NJ], jb2[NJ], jslider[NJ];
   float anchor1[NJ][3], anchor2[NJ][3], axis1[NJ][3], axis2[NJ][3], qrel[NJ][4], offset[NJ][3];
   float lostop[NJ], histop[NJ];
-  float ring[50][2];                   // tire sphere centres in the wheel frame
+  float ring[50][3];                   // tire sphere centres in the wheel frame (z = 0)
   float sphere_r;
   int ns_type[NNS], ns_body[NNS];      // 1 = box, 2 = cylinder
   float ns_off[NNS][3];                // geom offset position (body frame)
-  int ns_rot[NNS];                     // 1: offset rotation dRFromEulerAngles(pi/2,0,0)
+  int ns_rot[NNS];                     // 1: has an offset rotation
+  float ns_offR[NNS][9];               // dRFromEulerAngles(pi/2,0,0) as built in double by libm, cast to float
   float ns_dim[NNS][3];                // box sides | (radius, length, -)
   int ns_cb[NNS];                      // carries the Rover_1_tf fork callback
   float ft_ocA[2][3], ft_ocB[2][3];
   float getpos_rel[3];
   float step_side[2][3];
-  float robot_max_speed;
 };
 
 struct HfParams {

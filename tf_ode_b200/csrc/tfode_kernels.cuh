@@ -41,7 +41,7 @@ __device__ void reset_env(WarpSm& S, const StepParams& P, uint32_t env_global, u
     c.cr_dtorque_dt = (double)(2 * amp / cfg.crawler_dt_torque);
     // step box 0: dRFromEulerAngles(0,0,yaw) -> quaternion (ode/object.cc:116-121); fix joint frames (object.cc:155-179)
     double psi = yaw * 3.14159265358979323846 / 180.0;
-    double cp = cos(psi), sp = sin(psi);
+    double cp, sp; tfn::d_sincos(psi, &sp, &cp);
     double tr = 2 * cp + 1;  // |yaw| < 120 deg
     double s = sqrt(tr + 1), q0 = 0.5 * s, q3 = (-sp - sp) * (0.5 / s);
     double nrm = 1.0 / sqrt(q0 * q0 + q3 * q3); q0 *= nrm; q3 *= nrm;
@@ -98,12 +98,12 @@ __device__ void append_transition(const StepParams& P, const Ctrl& c, uint32_t e
 __device__ void get_state17(const WarpSm& S, float* s) {
   const float* R = S.bR[0];
   float vx0 = R[0], vx1 = R[3], vx2 = R[6];  // body x axis in the world
-  float direction = asinf(vx1) * 57.29577951308232f;
+  float direction = tfn::asin(vx1) * 57.29577951308232f;
   if (vx0 < 0) direction = (vx1 > 0 ? 1.0f : -1.0f) * 180.0f - direction;
   s[0] = direction;
   s[1] = S.c.jq_angle[1] * 57.29577951308232f;
-  s[2] = asinf(R[7]) * 57.29577951308232f;   // body y axis, z component
-  s[3] = asinf(-vx2) * 57.29577951308232f;
+  s[2] = tfn::asin(R[7]) * 57.29577951308232f;   // body y axis, z component
+  s[3] = tfn::asin(-vx2) * 57.29577951308232f;
   s[4] = S.c.jq_angle[2] * 57.29577951308232f;
   for (int i = 0; i < 12; i++) s[5 + i] = S.c.ft[i];
 }
@@ -173,10 +173,10 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       if (lane == 0) {
         Ctrl& c = S.c;
         c.done_step = 0;
-        if (P.ext_speed) c.robot_speed = fmin(fmax(-(double)M.robot_max_speed, (double)ext_speed), (double)M.robot_max_speed);
+        if (P.ext_speed) c.robot_speed = fmin(fmax(-M.robot_max_speed, (double)ext_speed), M.robot_max_speed);
         else if (cfg.term > 0 && fabsf(c.speed) <= fabsf(cfg.speedf)) {
           c.speed += cfg.speedf / cfg.term * cfg.dt;
-          c.robot_speed = fmin(fmax(-(double)M.robot_max_speed, (double)c.speed), (double)M.robot_max_speed);
+          c.robot_speed = fmin(fmax(-M.robot_max_speed, (double)c.speed), M.robot_max_speed);
         }
         float timef = (float)c.time_steps * cfg.dt;
         if (!c.ic_activated && cfg.ic_start >= 0 && (double)timef >= (double)c.ic_start) c.ic_activated = 1;
@@ -202,9 +202,12 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
               const float* bR = S.bR[gbody];
               mulRv(gp, bR, M.ns_off[g]);
               gp[0] += S.bpos[gbody][0]; gp[1] += S.bpos[gbody][1]; gp[2] += S.bpos[gbody][2];
-              if (M.ns_rot[g]) {  // R * [[1,0,0],[0,0,1],[0,-1,0]] : columns (c0, -c2, c1)
+              if (M.ns_rot[g]) {  // body rotation x geom offset rotation (dGeomSetOffsetRotation, src/rover_1.cc:158-159)
+                const float* oR = M.ns_offR[g];
 #pragma unroll
-                for (int r = 0; r < 3; r++) { gR[r * 3 + 0] = bR[r * 3 + 0]; gR[r * 3 + 1] = -bR[r * 3 + 2]; gR[r * 3 + 2] = bR[r * 3 + 1]; }
+                for (int r = 0; r < 3; r++)
+#pragma unroll
+                  for (int cc = 0; cc < 3; cc++) gR[r * 3 + cc] = tfn::dot3(bR[r * 3], bR[r * 3 + 1], bR[r * 3 + 2], oR[cc], oR[3 + cc], oR[6 + cc]);
               } else {
 #pragma unroll
                 for (int k = 0; k < 9; k++) gR[k] = bR[k];
@@ -248,8 +251,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
               const int w = s / 50, k = s - w * 50;
               gbody = 6 + w; soft = (k == 49);
               const float* bR = S.bR[gbody];
-              const float rx = M.ring[k][0], ry = M.ring[k][1];
-              float c[3] = {S.bpos[gbody][0] + bR[0] * rx + bR[1] * ry, S.bpos[gbody][1] + bR[3] * rx + bR[4] * ry, S.bpos[gbody][2] + bR[6] * rx + bR[7] * ry};
+              float c[3];
+              mulRv(c, bR, M.ring[k]);  // dBodyGetRelPointPos of the geom offset (ode/wheel.hh:70-72)
+              c[0] += S.bpos[gbody][0]; c[1] += S.bpos[gbody][1]; c[2] += S.bpos[gbody][2];
               if (tkind == T_PLANE) n = col_sphere_plane(c, M.sphere_r, cg);
               else if (tkind == T_BOX) n = col_sphere_box(c, M.sphere_r, tpos, tR, tside, cg);
               else n = col_sphere_hf(P.hf, c, M.sphere_r, cg);
@@ -296,14 +300,16 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       float iI[6] = {0, 0, 0, 0, 0, 0};  // xx xy xz yy yz zz
       if (body_lane) {
         const float i0 = M.invIb[lane][0], i1 = M.invIb[lane][1], i2 = M.invIb[lane][2];
-        iI[0] = R[0] * (i0 * R[0]) + R[1] * (i1 * R[1]) + R[2] * (i2 * R[2]);
-        iI[1] = R[0] * (i0 * R[3]) + R[1] * (i1 * R[4]) + R[2] * (i2 * R[5]);
-        iI[2] = R[0] * (i0 * R[6]) + R[1] * (i1 * R[7]) + R[2] * (i2 * R[8]);
-        iI[3] = R[3] * (i0 * R[3]) + R[4] * (i1 * R[4]) + R[5] * (i2 * R[5]);
-        iI[4] = R[3] * (i0 * R[6]) + R[4] * (i1 * R[7]) + R[5] * (i2 * R[8]);
-        iI[5] = R[6] * (i0 * R[6]) + R[7] * (i1 * R[7]) + R[8] * (i2 * R[8]);
-        // gyroscopic: tacc -= w x (I w), I w = R diag(Ib) R^T w
-        float wl[3] = {R[0] * avel[0] + R[3] * avel[1] + R[6] * avel[2], R[1] * avel[0] + R[4] * avel[1] + R[7] * avel[2], R[2] * avel[0] + R[5] * avel[1] + R[8] * avel[2]};
+        {
+          int n = 0;
+#pragma unroll
+          for (int r = 0; r < 3; r++)
+#pragma unroll
+            for (int cc = r; cc < 3; cc++)
+              iI[n++] = tfn::fma(R[r * 3 + 2], i2 * R[cc * 3 + 2], tfn::fma(R[r * 3 + 1], i1 * R[cc * 3 + 1], R[r * 3 + 0] * (i0 * R[cc * 3 + 0])));
+        }
+        // gyroscopic: tacc -= w x (I w), I w = R (Ib .* (R^T w))
+        float wl[3]; mulRtv(wl, R, avel);
         wl[0] *= M.Ib[lane][0]; wl[1] *= M.Ib[lane][1]; wl[2] *= M.Ib[lane][2];
         float Iw[3]; mulRv(Iw, R, wl);
         float cr[3]; cross3(cr, avel, Iw);
@@ -311,9 +317,8 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         facc[2] += M.mass[lane] * -9.80665f;
         float* bt = S.btmp[lane];
         bt[0] = facc[0] * invMass + lvel[0] * fps; bt[1] = facc[1] * invMass + lvel[1] * fps; bt[2] = facc[2] * invMass + lvel[2] * fps;
-        bt[3] = iI[0] * tacc[0] + iI[1] * tacc[1] + iI[2] * tacc[2] + avel[0] * fps;
-        bt[4] = iI[1] * tacc[0] + iI[3] * tacc[1] + iI[4] * tacc[2] + avel[1] * fps;
-        bt[5] = iI[2] * tacc[0] + iI[4] * tacc[1] + iI[5] * tacc[2] + avel[2] * fps;
+        { float t3[3]; symMulV(t3, iI, tacc);
+          bt[3] = t3[0] + avel[0] * fps; bt[4] = t3[1] + avel[1] * fps; bt[5] = t3[2] + avel[2] * fps; }
         float* bi = S.binvI[lane];
 #pragma unroll
         for (int k = 0; k < 6; k++) bi[k] = iI[k];
@@ -465,18 +470,18 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         const int hdr = __float_as_int(Sr[RS_HDR]);
         const int b1 = hdr & 15, b2 = (hdr >> 4) & 15;
         const float* t1 = S.btmp[b1]; const float* i1 = S.binvI[b1];
-        float s = Jr[0] * t1[0] + Jr[1] * t1[1] + Jr[2] * t1[2] + Jr[3] * t1[3] + Jr[4] * t1[4] + Jr[5] * t1[5];
-        float ax = i1[0] * Jr[3] + i1[1] * Jr[4] + i1[2] * Jr[5], ay = i1[1] * Jr[3] + i1[3] * Jr[4] + i1[4] * Jr[5], az = i1[2] * Jr[3] + i1[4] * Jr[4] + i1[5] * Jr[5];
-        float diag = i1[6] * (Jr[0] * Jr[0] + Jr[1] * Jr[1] + Jr[2] * Jr[2]) + (ax * Jr[3] + ay * Jr[4] + az * Jr[5]);
+        float s = tfn::dot6(Jr, t1);
+        float a3[3]; symMulV(a3, i1, Jr + 3);
+        float diag = tfn::fma(i1[6], dot3(Jr, Jr), dot3(a3, Jr + 3));
         if (b2 < NB) {
           const float* t2 = S.btmp[b2]; const float* i2 = S.binvI[b2];
-          s += Jr[6] * t2[0] + Jr[7] * t2[1] + Jr[8] * t2[2] + Jr[9] * t2[3] + Jr[10] * t2[4] + Jr[11] * t2[5];
-          ax = i2[0] * Jr[9] + i2[1] * Jr[10] + i2[2] * Jr[11]; ay = i2[1] * Jr[9] + i2[3] * Jr[10] + i2[4] * Jr[11]; az = i2[2] * Jr[9] + i2[4] * Jr[10] + i2[5] * Jr[11];
-          diag += i2[6] * (Jr[6] * Jr[6] + Jr[7] * Jr[7] + Jr[8] * Jr[8]) + (ax * Jr[9] + ay * Jr[10] + az * Jr[11]);
+          s = s + tfn::dot6(Jr + 6, t2);
+          symMulV(a3, i2, Jr + 9);
+          diag = diag + tfn::fma(i2[6], dot3(Jr + 6, Jr + 6), dot3(a3, Jr + 9));
         }
         const float cfm_h = Sr[RS_ADCFM] * fps;
         const float Ad = cfg.sor_w / (diag + cfm_h);
-        Sr[RS_RHS] = Sr[RS_C] * fps - s;
+        Sr[RS_RHS] = tfn::fma(Sr[RS_C], fps, -s);
         Sr[RS_AD] = Ad;
         Sr[RS_ADCFM] = Ad * cfm_h;
       }
@@ -572,7 +577,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
           float rhs = 0, Ad = 0, Adcfm = 0, lo = 0, hi = 0, lam = 0;
           if (mine) {
             J0 = Jm[0]; J1 = Jm[1]; J2 = Jm[2]; J3 = Jm[3]; J4 = Jm[4]; J5 = Jm[5];
-            part = J0 * fc[0] + J1 * fc[1] + J2 * fc[2] + J3 * fc[3] + J4 * fc[4] + J5 * fc[5];
+            part = tfn::fma(J5, fc[5], tfn::fma(J4, fc[4], tfn::fma(J3, fc[3], tfn::fma(J2, fc[2], tfn::fma(J1, fc[1], J0 * fc[0])))));
             rhs = Sr[RS_RHS]; Ad = Sr[RS_AD]; Adcfm = Sr[RS_ADCFM]; lo = Sr[RS_LO]; hi = Sr[RS_HI]; lam = Sr[RS_LAM];
             if (fidx != 255) { hi = fabsf(hi * S.rowS[fidx][RS_LAM]); lo = -hi; }
           }
@@ -581,16 +586,16 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
           __syncwarp();
           if (mine) {
             if (is1 && b2 >= NB) other = 0.0f;
-            const float sum = is1 ? (part + other) : (other + part);
-            float delta = Ad * (rhs - sum) - lam * Adcfm;
+            const float sum = (is1 && b2 >= NB) ? part : (is1 ? (part + other) : (other + part));
+            float delta = tfn::fma(Ad, rhs - sum, -(lam * Adcfm));
             float nl = lam + delta;
             if (nl < lo) { delta = lo - lam; nl = lo; }
             else if (nl > hi) { delta = hi - lam; nl = hi; }
             if (is1) S.rowS[row][RS_LAM] = nl;
             const float dm = delta * invMass;
-            fc[0] += dm * J0; fc[1] += dm * J1; fc[2] += dm * J2;
-            const float ax = iI[0] * J3 + iI[1] * J4 + iI[2] * J5, ay = iI[1] * J3 + iI[3] * J4 + iI[4] * J5, az = iI[2] * J3 + iI[4] * J4 + iI[5] * J5;
-            fc[3] += delta * ax; fc[4] += delta * ay; fc[5] += delta * az;
+            fc[0] = tfn::fma(dm, J0, fc[0]); fc[1] = tfn::fma(dm, J1, fc[1]); fc[2] = tfn::fma(dm, J2, fc[2]);
+            const float ax = tfn::dot3(iI[0], iI[1], iI[2], J3, J4, J5), ay = tfn::dot3(iI[1], iI[3], iI[4], J3, J4, J5), az = tfn::dot3(iI[2], iI[4], iI[5], J3, J4, J5);
+            fc[3] = tfn::fma(delta, ax, fc[3]); fc[4] = tfn::fma(delta, ay, fc[4]); fc[5] = tfn::fma(delta, az, fc[5]);
           }
           __syncwarp();
         }
@@ -605,9 +610,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         float ht[3] = {tacc[0] * h, tacc[1] * h, tacc[2] * h};
 #pragma unroll
         for (int k = 0; k < 3; k++) lvel[k] += hm * facc[k];
-        avel[0] += iI[0] * ht[0] + iI[1] * ht[1] + iI[2] * ht[2];
-        avel[1] += iI[1] * ht[0] + iI[3] * ht[1] + iI[4] * ht[2];
-        avel[2] += iI[2] * ht[0] + iI[4] * ht[1] + iI[5] * ht[2];
+        { float t3[3]; symMulV(t3, iI, ht); avel[0] += t3[0]; avel[1] += t3[1]; avel[2] += t3[2]; }
 #pragma unroll
         for (int k = 0; k < 3; k++) pos[k] += h * lvel[k];
         float dq[4];
@@ -646,7 +649,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         float qr[4]; qmul(qr, qB, qi);
         float n = sqrtf(qr[1] * qr[1] + qr[2] * qr[2] + qr[3] * qr[3]);
         float angle, axis[3];
-        if (n != 0.0f) { angle = 2.0f * atan2f(n, fabsf(qr[0])); if (qr[0] < 0.0f) n = -n; axis[0] = qr[1] / n; axis[1] = qr[2] / n; axis[2] = qr[3] / n; }
+        if (n != 0.0f) { angle = 2.0f * tfn::atan2(n, fabsf(qr[0])); if (qr[0] < 0.0f) n = -n; axis[0] = qr[1] / n; axis[1] = qr[2] / n; axis[2] = qr[3] / n; }
         else { angle = 0; axis[0] = 1; axis[1] = 0; axis[2] = 0; }
         for (int k = 0; k < 3; k++) T[k] = angle * 1e3f * axis[k] + 1.0f * (S.bvel[B][3 + k] - S.bvel[A][3 + k]);
         for (int k = 0; k < 3; k++) { S.ftraw[lane * 6 + k] = F[k]; S.ftraw[lane * 6 + 3 + k] = T[k]; }
@@ -749,7 +752,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       const float gamma = c.jq_angle[1], dgamma = c.jq_rate[1];
       const float wb = 0.58f, wt = 0.61f, rs = (float)c.robot_speed, wr = 0.105f, WMS = 7.4351f;
       float diff[4], trans[4], min_speed = 0, adj;
-      const float tg = tanf(gamma / 2);
+      const float tg = tfn::tan(gamma / 2);
       const bool crawl = cfg.crawling_mode || cfg.controller == TFODE_CTRL_CRAWLER;
 #pragma unroll
       for (int i = 0; i < 4; i++) {
@@ -897,11 +900,11 @@ __global__ void observe_kernel(const EnvRec* rec, int n, float* obs17, float* re
     float q[4] = {r.body[F_QUAT + 0][0], r.body[F_QUAT + 1][0], r.body[F_QUAT + 2][0], r.body[F_QUAT + 3][0]};
     float R[9]; quatToR(R, q);
     float vx0 = R[0], vx1 = R[3], vx2 = R[6];
-    float direction = asinf(vx1) * 57.29577951308232f;
+    float direction = tfn::asin(vx1) * 57.29577951308232f;
     if (vx0 < 0) direction = (vx1 > 0 ? 1.0f : -1.0f) * 180.0f - direction;
     float* o = obs17 + (size_t)e * 17;
-    o[0] = direction; o[1] = r.c.jq_angle[1] * 57.29577951308232f; o[2] = asinf(R[7]) * 57.29577951308232f;
-    o[3] = asinf(-vx2) * 57.29577951308232f; o[4] = r.c.jq_angle[2] * 57.29577951308232f;
+    o[0] = direction; o[1] = r.c.jq_angle[1] * 57.29577951308232f; o[2] = tfn::asin(R[7]) * 57.29577951308232f;
+    o[3] = tfn::asin(-vx2) * 57.29577951308232f; o[4] = r.c.jq_angle[2] * 57.29577951308232f;
     for (int i = 0; i < 12; i++) o[5 + i] = r.c.ft[i];
   }
   if (reward) reward[e] = (float)r.c.last_reward;
@@ -946,7 +949,7 @@ __global__ void __launch_bounds__(256) policy_fp32_kernel(const float* __restric
     for (int r = 0; r < POL_ROWS; r++) acc[r] = b1[j];
     for (int i = 0; i < 17; i++) { float w = W1[i * 512 + j];
 #pragma unroll
-      for (int r = 0; r < POL_ROWS; r++) acc[r] += x[r][i] * w; }
+      for (int r = 0; r < POL_ROWS; r++) acc[r] = tfn::fma(x[r][i], w, acc[r]); }
 #pragma unroll
     for (int r = 0; r < POL_ROWS; r++) h1[r][j] = acc[r] > 0 ? acc[r] : 0;
   }
@@ -957,23 +960,20 @@ __global__ void __launch_bounds__(256) policy_fp32_kernel(const float* __restric
     for (int r = 0; r < POL_ROWS; r++) acc[r] = b2[j];
     for (int i = 0; i < 512; i++) { float w = W2[i * 512 + j];
 #pragma unroll
-      for (int r = 0; r < POL_ROWS; r++) acc[r] += h1[r][i] * w; }
+      for (int r = 0; r < POL_ROWS; r++) acc[r] = tfn::fma(h1[r][i], w, acc[r]); }
 #pragma unroll
     for (int r = 0; r < POL_ROWS; r++) h2[r][j] = acc[r] > 0 ? acc[r] : 0;
   }
   __syncthreads();
-  // layer 3: warp w handles rows w, w+8; sequential-order-independent tree sum
-  const int lane = t & 31, w = t >> 5;
-  for (int r = w; r < nr; r += 8) {
-    float s0 = 0, s1 = 0;
-    for (int i = lane; i < 512; i += 32) { s0 += h2[r][i] * W3[i * 2 + 0]; s1 += h2[r][i] * W3[i * 2 + 1]; }
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) { s0 += __shfl_xor_sync(FULLMASK, s0, d); s1 += __shfl_xor_sync(FULLMASK, s1, d); }
-    if (lane == 0) {
-      float a0 = tanhf(s0 + b3[0]), a1 = tanhf(s1 + b3[1]);
-      if (list) { EnvRec& e = rec[list[row0 + r]]; e.c.policy_act[0] = a0; e.c.policy_act[1] = a1; e.c.parked = 2; }
-      else { act_direct[(size_t)(row0 + r) * 2] = a0; act_direct[(size_t)(row0 + r) * 2 + 1] = a1; }
-    }
+  // layer 3: one thread per (row, output), accumulated in input order from the bias like the two layers above
+  // (the fp32 policy path is bit-reproducible; the tensor-core path is the fast one)
+  if (t < nr * 2) {
+    const int r = t >> 1, j = t & 1;
+    float s3 = b3[j];
+    for (int i = 0; i < 512; i++) s3 = tfn::fma(h2[r][i], W3[i * 2 + j], s3);
+    const float a = tfn::tanh(s3);
+    if (list) { EnvRec& e = rec[list[row0 + r]]; e.c.policy_act[j] = a; if (j == 0) e.c.parked = 2; }
+    else act_direct[(size_t)(row0 + r) * 2 + j] = a;
   }
 }
 __global__ void zero_int_kernel(int* p) { *p = 0; }

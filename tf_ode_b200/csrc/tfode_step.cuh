@@ -16,6 +16,7 @@
 #pragma once
 #include <math_constants.h>
 
+#include "../../include/tfode_numerics.h"
 #include "tfode_device.cuh"
 
 namespace tfode {
@@ -45,14 +46,17 @@ static_assert(sizeof(EnvRec) <= sizeof(float) * MAXROWS * 12, "record staging al
 enum { RS_RHS = 0, RS_AD = 1, RS_ADCFM = 2, RS_LO = 3, RS_HI = 4, RS_LAM = 5, RS_HDR = 6, RS_C = 7 };
 
 // ---------------------------------------------------------------- small math
-__device__ __forceinline__ float dot3(const float* a, const float* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
-__device__ __forceinline__ void cross3(float* r, const float* a, const float* b) {
-  r[0] = a[1] * b[2] - a[2] * b[1]; r[1] = a[2] * b[0] - a[0] * b[2]; r[2] = a[0] * b[1] - a[1] * b[0];
-}
-__device__ __forceinline__ void mulRv(float* r, const float* R, const float* v) {  // R: 3 rows of stride 3
-  r[0] = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
-  r[1] = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
-  r[2] = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
+// fma placement of these products is fixed by the numerics contract (include/tfode_numerics.h); the kernels are
+// compiled with -fmad=false, so every other expression below is evaluated exactly as written.
+__device__ __forceinline__ float dot3(const float* a, const float* b) { return tfn::dot3(a, b); }
+__device__ __forceinline__ void cross3(float* r, const float* a, const float* b) { tfn::cross3(r, a, b); }
+__device__ __forceinline__ void mulRv(float* r, const float* R, const float* v) { tfn::mulRv(r, R, v, 3); }    // R: 3 rows of stride 3
+__device__ __forceinline__ void mulRtv(float* r, const float* R, const float* v) { tfn::mulRtv(r, R, v, 3); }
+__device__ __forceinline__ void symMulV(float* r, const float* S, const float* v) {  // S = xx xy xz yy yz zz
+  float a = tfn::dot3(S[0], S[1], S[2], v[0], v[1], v[2]);
+  float b = tfn::dot3(S[1], S[3], S[4], v[0], v[1], v[2]);
+  float c = tfn::dot3(S[2], S[4], S[5], v[0], v[1], v[2]);
+  r[0] = a; r[1] = b; r[2] = c;
 }
 __device__ __forceinline__ void quatToR(float* R, const float* q) {
   float qq1 = 2 * q[1] * q[1], qq2 = 2 * q[2] * q[2], qq3 = 2 * q[3] * q[3];
@@ -144,9 +148,7 @@ __device__ __forceinline__ int col_sphere_plane(const float* c, float r, CG* out
 __device__ __forceinline__ int col_sphere_box(const float* c, float r, const float* bpos, const float* bR, const float* side, CG* out) {
   float p[3] = {c[0] - bpos[0], c[1] - bpos[1], c[2] - bpos[2]}, l[3], t[3];
   bool onborder = false;
-  t[0] = bR[0] * p[0] + bR[3] * p[1] + bR[6] * p[2];
-  t[1] = bR[1] * p[0] + bR[4] * p[1] + bR[7] * p[2];
-  t[2] = bR[2] * p[0] + bR[5] * p[1] + bR[8] * p[2];
+  mulRtv(t, bR, p);
 #pragma unroll
   for (int i = 0; i < 3; i++) {
     l[i] = side[i] * 0.5f;
@@ -255,9 +257,7 @@ __device__ int col_box_plane(const float* bpos, const float* R, const float* sid
 // sample point strictly inside a terrain box -> pushed out through the nearest face
 __device__ __forceinline__ bool point_in_box(const float* p, const float* bpos, const float* bR, const float* side, float* nrm, float* depth) {
   float d[3] = {p[0] - bpos[0], p[1] - bpos[1], p[2] - bpos[2]}, t[3];
-  t[0] = bR[0] * d[0] + bR[3] * d[1] + bR[6] * d[2];
-  t[1] = bR[1] * d[0] + bR[4] * d[1] + bR[7] * d[2];
-  t[2] = bR[2] * d[0] + bR[5] * d[1] + bR[8] * d[2];
+  mulRtv(t, bR, d);
   float best = CUDART_INF_F; int mini = -1;
 #pragma unroll
   for (int i = 0; i < 3; i++) {
@@ -297,7 +297,7 @@ __device__ __forceinline__ bool point_vs_hf(const HfParams& hf, const float* pw,
 }
 
 // sphere vs heightfield: local minima of the centre-to-surface distance (faces, convex edges, convex
-// vertices); scan order and tests as oracle/ode_restated.hpp collideSphereHF (DESIGN.md D-HF).
+// vertices); scan order and tests: DESIGN.md D-HF.
 __device__ int col_sphere_hf(const HfParams& hf, const float* cw, float r, CG* out) {
   float c[3]; hf_to_local(hf, cw, c);
   int ix0 = (int)floorf((c[0] - r) * hf.inv_sx), ix1 = (int)floorf((c[0] + r) * hf.inv_sx);
@@ -461,8 +461,8 @@ __device__ __forceinline__ float hinge_angle(const WarpSm& S, int j) {
   qmul_inv_b(qerr, qq, M.qrel[j]);
   float cost2 = qerr[0];
   float sint2 = sqrtf(qerr[1] * qerr[1] + qerr[2] * qerr[2] + qerr[3] * qerr[3]);
-  float d = qerr[1] * M.axis1[j][0] + qerr[2] * M.axis1[j][1] + qerr[3] * M.axis1[j][2];
-  float theta = (d >= 0) ? (2 * atan2f(sint2, cost2)) : (2 * atan2f(sint2, -cost2));
+  float d = dot3(qerr + 1, M.axis1[j]);
+  float theta = (d >= 0) ? (2 * tfn::atan2(sint2, cost2)) : (2 * tfn::atan2(sint2, -cost2));
   if (theta > 3.14159265358979323846f) theta -= 6.28318530717958647692f;
   return -theta;
 }
