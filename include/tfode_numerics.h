@@ -52,10 +52,8 @@ TFN_HD double fma(double a, double b, double c) {
 // a0*b0 + a1*b1 + a2*b2 as  fma(a2,b2, fma(a1,b1, a0*b0))
 template <class T> TFN_HD T dot3(const T* a, const T* b) { return fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0])); }
 template <class T> TFN_HD T dot3(T a0, T a1, T a2, T b0, T b1, T b2) { return fma(a2, b2, fma(a1, b1, a0 * b0)); }
-// six-term dot product, same left-to-right chaining
-template <class T> TFN_HD T dot6(const T* a, const T* b) {
-  return fma(a[5], b[5], fma(a[4], b[4], fma(a[3], b[3], fma(a[2], b[2], fma(a[1], b[1], a[0] * b[0])))));
-}
+// six-term dot product (a Jacobian half-row against a body's 6-vector): linear triple + angular triple
+template <class T> TFN_HD T dot6(const T* a, const T* b) { return dot3(a, b) + dot3(a + 3, b + 3); }
 // a x b with each component as fma(a_i, b_j, -(a_j * b_i))
 template <class T> TFN_HD void cross3(T* r, const T* a, const T* b) {
   T x = fma(a[1], b[2], -(a[2] * b[1]));

@@ -179,7 +179,7 @@ def test_policy_infer_is_bit_exact_with_oracle_fp32_path():
 # ----------------------------------------------------------------------------------------------------------------------
 def test_transitions_match_oracle_rows():
     n = 32
-    g, o = make_pair("training_fast", n)
+    g, o = make_pair("training_fast", n, transition_capacity=8 * n * 10)
     g.step(5000); o.step(5000)
     buf = torch.zeros(8 * n * 10, abi.TRANSITION_WIDTH, device="cuda")
     cnt = g.drain_transitions(buf, buf.shape[0])
@@ -190,6 +190,7 @@ def test_transitions_match_oracle_rows():
     for e in range(n):
         a = rows_g[rows_g[:, 0] == e]; b = rows_o[rows_o[:, 0] == e]
         assert np.array_equal(a, b), "env %d" % e
+    assert rows_g[:, 21].sum() > 0  # episodes ended: terminal flag patched into the last tuple (rover_training_1.cc:212-224)
     g.close(); o.close()
 
 

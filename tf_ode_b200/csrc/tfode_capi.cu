@@ -34,7 +34,7 @@ struct TfodeBatch {
   float* d_obs = nullptr; float* d_rew = nullptr; uint8_t* d_done = nullptr; float* d_act = nullptr;
   float* h_pin = nullptr; size_t h_pin_bytes = 0;
   int* d_ids = nullptr; int ids_cap = 0;
-  size_t smem_bytes = 0;
+  size_t smem_bytes = 0, smem_step = 0;
 };
 
 #define CK(call)                                                                            \
@@ -317,7 +317,8 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   }
   b->cfg.hf_heights = nullptr;
   b->smem_bytes = sizeof(WarpSm) * WARPS_PER_CTA;
-  CKC(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
+  b->smem_step = sizeof(WarpSm) * ENVS_PER_CTA;
+  CKC(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
   if (launch_reset(b, nullptr, n, 1) != TFODE_OK) return fail(TFODE_ECUDA);
   CKC(cudaStreamSynchronize(b->stream));
@@ -414,7 +415,7 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
   for (int r = 0; r < rounds; r++) {
     StepParams P = b->P;
     P.set_budget = (r == 0) ? n_substeps : -1;
-    step_kernel<<<launch_blocks(n), WARPS_PER_CTA * 32, b->smem_bytes, b->stream>>>(P);
+    step_kernel<<<(n + ENVS_PER_CTA - 1) / ENVS_PER_CTA, ENVS_PER_CTA * 32, b->smem_step, b->stream>>>(P);
     b->launches++;
     CK(cudaGetLastError());
     if (mlp) {

@@ -33,6 +33,7 @@ struct Ctrl {
   double total_reward, last_reward;
   double last_pos[3];
   double cr_dtorque_dt;
+  double pending_reward;   // reward of the held-back tuple (fp64 until the terminal penalty is known)
   long long time_steps;    // Sim_loop::_time
   float wheel_vel[4], wheel_fmax[4], W[4];
   float servo_vel;

@@ -4,7 +4,8 @@
 
 namespace tfode {
 
-constexpr int WARPS_PER_CTA = 4;
+constexpr int WARPS_PER_CTA = 4;   // reset kernel
+constexpr int ENVS_PER_CTA = 8;    // step kernel: 8 environments = 8 warps per CTA, 2 CTAs per SM
 
 // warp-inclusive scan of small counts
 __device__ __forceinline__ int warp_incl_scan(int v, int lane) {
@@ -89,7 +90,7 @@ __device__ void append_transition(const StepParams& P, const Ctrl& c, uint32_t e
   row[0] = (float)env_global;
   for (int i = 0; i < 17; i++) row[1 + i] = c.pending[i];
   row[18] = c.pending[17]; row[19] = c.pending[18];
-  row[20] = c.pending[19] - penalty; row[21] = terminal ? 1.0f : 0.0f;
+  row[20] = (float)(c.pending_reward - (double)penalty); row[21] = terminal ? 1.0f : 0.0f;
   for (int i = 0; i < 17; i++) row[22 + i] = c.pending[20 + i];
   for (int i = 39; i < TFODE_TRANSITION_WIDTH; i++) row[i] = 0;
 }
@@ -110,48 +111,154 @@ __device__ void get_state17(const WarpSm& S, float* s) {
 
 // ================================================================================================
 //                                         THE STEP KERNEL
+// One CTA = ENVS_PER_CTA environments.  Collision, row construction, integration and the rover's control
+// code run with one warp per environment (lane = body / geom / joint / row).  The Gauss-Seidel sweeps,
+// which are sequential inside a constraint island, run "packed": warp 0 of the CTA gives every island of
+// every environment its own lane (4 lanes per environment), so a sweep instruction serves up to 32 islands.
 // ================================================================================================
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepParams P) {
+
+// One row relaxation of SOR_LCP (quickstep.cpp) for the island this lane owns; everything in shared memory.
+__device__ __forceinline__ void pgs_row_update(WarpSm& S, int row) {
+  const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);   // rhs Ad Adcfm lo
+  const float4 s1 = *reinterpret_cast<const float4*>(&S.rowS[row][4]);   // hi lam hdr -
+  const int hdr = __float_as_int(s1.z);
+  const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
+  const bool has2 = b2 < NB;
+  float J[12];
+  {
+    const float4* Jp = reinterpret_cast<const float4*>(&S.rowJ[row][0]);
+    const float4 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
+    J[0] = j0.x; J[1] = j0.y; J[2] = j0.z; J[3] = j0.w; J[4] = j1.x; J[5] = j1.y; J[6] = j1.z; J[7] = j1.w; J[8] = j2.x; J[9] = j2.y; J[10] = j2.z; J[11] = j2.w;
+  }
+  float f1[6], f2[6];
+  {
+    const float4 a = *reinterpret_cast<const float4*>(&S.btmp[b1][0]); const float2 b = *reinterpret_cast<const float2*>(&S.btmp[b1][4]);
+    f1[0] = a.x; f1[1] = a.y; f1[2] = a.z; f1[3] = a.w; f1[4] = b.x; f1[5] = b.y;
+  }
+  float sum = tfn::dot6(J, f1);
+  if (has2) {
+    const float4 a = *reinterpret_cast<const float4*>(&S.btmp[b2][0]); const float2 b = *reinterpret_cast<const float2*>(&S.btmp[b2][4]);
+    f2[0] = a.x; f2[1] = a.y; f2[2] = a.z; f2[3] = a.w; f2[4] = b.x; f2[5] = b.y;
+    sum = sum + tfn::dot6(J + 6, f2);
+  }
+  float lo = s0.w, hi = s1.x;
+  const float lam = s1.y;
+  if (fidx != 255) { hi = fabsf(hi * S.rowS[fidx][RS_LAM]); lo = -hi; }
+  float delta = tfn::fma(s0.y, s0.x - sum, -(lam * s0.z));
+  float nl = lam + delta;
+  if (nl < lo) { delta = lo - lam; nl = lo; }
+  else if (nl > hi) { delta = hi - lam; nl = hi; }
+  S.rowS[row][RS_LAM] = nl;
+  {
+    const float4 ia = *reinterpret_cast<const float4*>(&S.binvI[b1][0]); const float4 ib = *reinterpret_cast<const float4*>(&S.binvI[b1][4]);
+    const float dm = delta * ib.z;
+    const float ax = tfn::dot3(ia.x, ia.y, ia.z, J[3], J[4], J[5]), ay = tfn::dot3(ia.y, ia.w, ib.x, J[3], J[4], J[5]), az = tfn::dot3(ia.z, ib.x, ib.y, J[3], J[4], J[5]);
+    float4 o; float2 o2;
+    o.x = tfn::fma(dm, J[0], f1[0]); o.y = tfn::fma(dm, J[1], f1[1]); o.z = tfn::fma(dm, J[2], f1[2]);
+    o.w = tfn::fma(delta, ax, f1[3]); o2.x = tfn::fma(delta, ay, f1[4]); o2.y = tfn::fma(delta, az, f1[5]);
+    *reinterpret_cast<float4*>(&S.btmp[b1][0]) = o; *reinterpret_cast<float2*>(&S.btmp[b1][4]) = o2;
+  }
+  if (has2) {
+    const float4 ia = *reinterpret_cast<const float4*>(&S.binvI[b2][0]); const float4 ib = *reinterpret_cast<const float4*>(&S.binvI[b2][4]);
+    const float dm = delta * ib.z;
+    const float ax = tfn::dot3(ia.x, ia.y, ia.z, J[9], J[10], J[11]), ay = tfn::dot3(ia.y, ia.w, ib.x, J[9], J[10], J[11]), az = tfn::dot3(ia.z, ib.x, ib.y, J[9], J[10], J[11]);
+    float4 o; float2 o2;
+    o.x = tfn::fma(dm, J[6], f2[0]); o.y = tfn::fma(dm, J[7], f2[1]); o.z = tfn::fma(dm, J[8], f2[2]);
+    o.w = tfn::fma(delta, ax, f2[3]); o2.x = tfn::fma(delta, ay, f2[4]); o2.y = tfn::fma(delta, az, f2[5]);
+    *reinterpret_cast<float4*>(&S.btmp[b2][0]) = o; *reinterpret_cast<float2*>(&S.btmp[b2][4]) = o2;
+  }
+}
+
+// Sweeps of all environments of the CTA, one lane per island: lane = 4*slot + i; i = 0,1,2 own island labels
+// 0,1,2 (chassis group, front axle, rear axle, each possibly merged with a step box), i = 3 owns labels 3 and 4
+// (the step boxes when nothing touches them).  Every island draws its Fisher-Yates swaps from its own slice of
+// the environment's dRand() stream, exactly as a sequential island-by-island solve would.
+__device__ void pgs_packed(WarpSm* sm, int pgs_iters, int lane) {
+  const int e = lane >> 2, i = lane & 3;
+  WarpSm& S = sm[e];
+  const bool on = e < ENVS_PER_CTA && S.pgs_on != 0;
+  int off = 0, m0 = 0, m1 = 0, base0 = 0, base1 = 0;
+  uint32_t seed0 = 0;
+  if (on) {
+    seed0 = S.c.lcg_seed;
+    off = S.isl_off[i]; m0 = S.isl_m[i]; base0 = S.isl_base[i];
+    if (i == 3) { m1 = S.isl_m[4]; base1 = S.isl_base[4]; }
+  }
+  const int m = m0 + m1;
+  const int maxm = __reduce_max_sync(FULLMASK, m);
+  unsigned char* ord = S.order + off;
+  for (int it = 0; it < pgs_iters; it++) {
+    if ((it & 7) == 0) {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt
+#pragma unroll 1
+      for (int sg = 0; sg < 2; sg++) {
+        const int mm = sg ? m1 : m0;
+        if (mm > 1) {
+          unsigned char* o = ord + (sg ? m0 : 0);
+          uint32_t sd = lcg_jump(seed0, (uint32_t)((sg ? base1 : base0) + (it >> 3) * (mm - 1)));
+          for (int q = 1; q < mm; q++) {
+            const int sw = lcg_randint(sd, (uint32_t)(q + 1));
+            const unsigned char a = o[q], b = o[sw];
+            o[q] = b; o[sw] = a;
+          }
+        }
+      }
+    }
+#pragma unroll 1
+    for (int k = 0; k < maxm; k++)
+      if (k < m) pgs_row_update(S, ord[k]);
+  }
+}
+
+__global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int env = blockIdx.x * WARPS_PER_CTA + wid;
-  if (env >= P.n_envs) return;
-  WarpSm& S = reinterpret_cast<WarpSm*>(smem_raw)[wid];
+  const int env = blockIdx.x * ENVS_PER_CTA + wid;
+  const bool valid = env < P.n_envs;
+  WarpSm* const sm = reinterpret_cast<WarpSm*>(smem_raw);
+  WarpSm& S = sm[wid];
   const Model& M = g_model;
   const TfodeBatchConfig& cfg = P.cfg;
   const uint32_t env_global = (uint32_t)(cfg.env_id_offset + env);
 
-  int budget = (P.set_budget >= 0) ? P.set_budget : P.budget[env];
-  if (budget <= 0 && P.set_budget < 0) return;
+  int budget = 0;
+  if (valid) budget = (P.set_budget >= 0) ? P.set_budget : P.budget[env];
+  if (lane == 0) { S.pgs_on = 0; S.c.frozen = 0; S.c.parked = 0; }
 
   // ---------------------------------------------------------------- load the record (coalesced float4 -> smem staging -> registers)
-  EnvRec* grec = P.rec + env;
-  {
-    const float4* src = reinterpret_cast<const float4*>(grec);
-    float4* dst = reinterpret_cast<float4*>(&S.rowJ[0][0]);
-    constexpr int N4 = sizeof(EnvRec) / 16;
-    for (int i = lane; i < N4; i += 32) dst[i] = src[i];
-  }
-  __syncwarp();
+  EnvRec* grec = P.rec + (valid ? env : 0);
   float pos[3], q[4], R[9], lvel[3], avel[3], facc[3], tacc[3];
-  {
-    const EnvRec* st = reinterpret_cast<const EnvRec*>(&S.rowJ[0][0]);
-    const int b = lane < NB ? lane : 0;
+  if (valid) {
+    {
+      const float4* src = reinterpret_cast<const float4*>(grec);
+      float4* dst = reinterpret_cast<float4*>(&S.rowJ[0][0]);
+      constexpr int N4 = sizeof(EnvRec) / 16;
+      for (int i = lane; i < N4; i += 32) dst[i] = src[i];
+    }
+    __syncwarp();
+    {
+      const EnvRec* st = reinterpret_cast<const EnvRec*>(&S.rowJ[0][0]);
+      const int b = lane < NB ? lane : 0;
 #pragma unroll
-    for (int k = 0; k < 3; k++) { pos[k] = st->body[F_POS + k][b]; lvel[k] = st->body[F_LVEL + k][b]; avel[k] = st->body[F_AVEL + k][b]; facc[k] = st->body[F_FACC + k][b]; tacc[k] = st->body[F_TACC + k][b]; }
+      for (int k = 0; k < 3; k++) { pos[k] = st->body[F_POS + k][b]; lvel[k] = st->body[F_LVEL + k][b]; avel[k] = st->body[F_AVEL + k][b]; facc[k] = st->body[F_FACC + k][b]; tacc[k] = st->body[F_TACC + k][b]; }
 #pragma unroll
-    for (int k = 0; k < 4; k++) q[k] = st->body[F_QUAT + k][b];
-    const uint32_t* cs = reinterpret_cast<const uint32_t*>(&st->c);
-    uint32_t* cd = reinterpret_cast<uint32_t*>(&S.c);
-    for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
+      for (int k = 0; k < 4; k++) q[k] = st->body[F_QUAT + k][b];
+      const uint32_t* cs = reinterpret_cast<const uint32_t*>(&st->c);
+      uint32_t* cd = reinterpret_cast<uint32_t*>(&S.c);
+      for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
+    }
+    __syncwarp();
+    if (P.set_budget >= 0 && lane == 0) S.c.done_call = 0;
+    quatToR(R, q);
+    publish_body(S, lane, pos, q, R, lvel, avel);
+    __syncwarp();
+    joint_readouts(S, lane);  // derived from the pose: recomputed so that records written by set_state are consistent
+    __syncwarp();
+  } else {
+#pragma unroll
+    for (int k = 0; k < 3; k++) { pos[k] = 0; lvel[k] = 0; avel[k] = 0; facc[k] = 0; tacc[k] = 0; }
+    q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0;
+    quatToR(R, q);
   }
-  __syncwarp();
-  if (P.set_budget >= 0 && lane == 0) S.c.done_call = 0;
-  quatToR(R, q);
-  publish_body(S, lane, pos, q, R, lvel, avel);
-  __syncwarp();
-  joint_readouts(S, lane);  // derived from the pose: recomputed so that records written by set_state are consistent
-  __syncwarp();
 
   const int nb_active = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? NB : NBR;
   const int nj_active = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? NJ : NJ - 2;
@@ -159,14 +266,17 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
   const float h = cfg.dt;
   const float fps = 1.0f / h;
   const float invMass = body_lane ? M.invMass[lane] : 0.0f;
-  const float ext_speed = P.ext_speed ? P.ext_speed[env] : 0.0f;
+  const float ext_speed = (valid && P.ext_speed) ? P.ext_speed[env] : 0.0f;
   const int maxc = min(cfg.max_contacts, MAXC);
+  float iI[6] = {0, 0, 0, 0, 0, 0};  // world inverse inertia of my body: xx xy xz yy yz zz
 
-  // ================================================================== sub-step loop
-  while (budget > 0) {
-    if (S.c.frozen) { budget = 0; break; }
-    bool do_part_a = S.c.parked == 0;
-    if (S.c.parked == 1) break;  // still waiting for the policy kernel (should not happen inside a call)
+  // ================================================================== sub-step loop (CTA-uniform trip count)
+  for (;;) {
+    __syncwarp();
+    if (valid && S.c.frozen) budget = 0;
+    const bool runnable = valid && budget > 0 && S.c.parked != 1;
+    if (!__syncthreads_or(runnable ? 1 : 0)) break;
+    const bool do_part_a = runnable && S.c.parked == 0;
 
     if (do_part_a) {
       // ------------------------------------------------------------ scene lambda prologue (rover_training_1.cc:129-136)
@@ -297,7 +407,6 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       }
 
       // ------------------------------------------------------------ per-body prep: world inverse inertia, gyroscopic torque, gravity, v/h + invM f
-      float iI[6] = {0, 0, 0, 0, 0, 0};  // xx xy xz yy yz zz
       if (body_lane) {
         const float i0 = M.invIb[lane][0], i1 = M.invIb[lane][1], i2 = M.invIb[lane][2];
         {
@@ -507,7 +616,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       { int acc = 0, draws = 0;
 #pragma unroll
         for (int L = 0; L < NISL; L++) { mL[L] = cntN[L] + cntF[L]; offL[L] = acc; acc += mL[L]; baseL[L] = draws; draws += nshuf * max(mL[L] - 1, 0); }
-        if (lane == 0) { S.aux[8] = __int_as_float(draws); S.c.n_rows = m_total; }
+        if (lane == 0) { S.n_draws = draws; S.c.n_rows = m_total; }
+#pragma unroll
+        for (int L = 0; L < NISL; L++) if (lane == L) { S.isl_off[L] = offL[L]; S.isl_m[L] = mL[L]; S.isl_base[L] = baseL[L]; }
       }
       {
         int pN[NISL], pF[NISL];
@@ -532,78 +643,27 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
           }
         }
       }
-      // my island (as a body lane)
-      int my_off = 0, my_m = 0, my_base = 0; bool leader = false;
-      if (body_lane) {
-        const int g = body_group(lane);
-        int lab = 0;
-#pragma unroll
-        for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L];
-#pragma unroll
-        for (int L = 0; L < NISL; L++) if (lab == L) { my_off = offL[L]; my_m = mL[L]; my_base = baseL[L]; }
-        const int first_body = (lab == 0) ? 0 : (lab == 1 ? 4 : (lab == 2 ? 5 : (lab == 3 ? 10 : 11)));
-        leader = lane == first_body;
-      }
-      int maxm = 0;
-#pragma unroll
-      for (int L = 0; L < NISL; L++) maxm = max(maxm, mL[L]);
       __syncwarp();
 
-      // ------------------------------------------------------------ PGS / SOR sweeps
-      float fc[6] = {0, 0, 0, 0, 0, 0};
-      const uint32_t seed0 = S.c.lcg_seed;
-      for (int it = 0; it < cfg.pgs_iters; it++) {
-        if ((it & 7) == 0) {
-          if (leader && my_m > 1) {  // Fisher-Yates with ODE's dRandInt, this island's slice of the env's LCG stream
-            uint32_t sd = lcg_jump(seed0, (uint32_t)(my_base + (it >> 3) * (my_m - 1)));
-            for (int i = 1; i < my_m; i++) {
-              int sw = lcg_randint(sd, (uint32_t)(i + 1));
-              unsigned char a = S.order[my_off + i], b = S.order[my_off + sw];
-              S.order[my_off + i] = b; S.order[my_off + sw] = a;
-            }
-          }
-          __syncwarp();
-        }
-        for (int k = 0; k < maxm; k++) {
-          const bool act = body_lane && k < my_m;
-          const int row = act ? S.order[my_off + k] : 0;
-          const float* Sr = S.rowS[row];
-          const int hdr = __float_as_int(Sr[RS_HDR]);
-          const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
-          const bool is1 = act && lane == b1, is2 = act && lane == b2;
-          const bool mine = is1 || is2;
-          const float* Jm = S.rowJ[row] + (is2 ? 6 : 0);
-          float J0 = 0, J1 = 0, J2 = 0, J3 = 0, J4 = 0, J5 = 0, part = 0;
-          float rhs = 0, Ad = 0, Adcfm = 0, lo = 0, hi = 0, lam = 0;
-          if (mine) {
-            J0 = Jm[0]; J1 = Jm[1]; J2 = Jm[2]; J3 = Jm[3]; J4 = Jm[4]; J5 = Jm[5];
-            part = tfn::fma(J5, fc[5], tfn::fma(J4, fc[4], tfn::fma(J3, fc[3], tfn::fma(J2, fc[2], tfn::fma(J1, fc[1], J0 * fc[0])))));
-            rhs = Sr[RS_RHS]; Ad = Sr[RS_AD]; Adcfm = Sr[RS_ADCFM]; lo = Sr[RS_LO]; hi = Sr[RS_HI]; lam = Sr[RS_LAM];
-            if (fidx != 255) { hi = fabsf(hi * S.rowS[fidx][RS_LAM]); lo = -hi; }
-          }
-          const int partner = is1 ? (b2 < NB ? b2 : lane) : (is2 ? b1 : lane);
-          float other = __shfl_sync(FULLMASK, part, partner);
-          __syncwarp();
-          if (mine) {
-            if (is1 && b2 >= NB) other = 0.0f;
-            const float sum = (is1 && b2 >= NB) ? part : (is1 ? (part + other) : (other + part));
-            float delta = tfn::fma(Ad, rhs - sum, -(lam * Adcfm));
-            float nl = lam + delta;
-            if (nl < lo) { delta = lo - lam; nl = lo; }
-            else if (nl > hi) { delta = hi - lam; nl = hi; }
-            if (is1) S.rowS[row][RS_LAM] = nl;
-            const float dm = delta * invMass;
-            fc[0] = tfn::fma(dm, J0, fc[0]); fc[1] = tfn::fma(dm, J1, fc[1]); fc[2] = tfn::fma(dm, J2, fc[2]);
-            const float ax = tfn::dot3(iI[0], iI[1], iI[2], J3, J4, J5), ay = tfn::dot3(iI[1], iI[3], iI[4], J3, J4, J5), az = tfn::dot3(iI[2], iI[4], iI[5], J3, J4, J5);
-            fc[3] = tfn::fma(delta, ax, fc[3]); fc[4] = tfn::fma(delta, ay, fc[4]); fc[5] = tfn::fma(delta, az, fc[5]);
-          }
-          __syncwarp();
-        }
+      if (lane < NB) {  // btmp becomes fc: the sweeps start from zero constraint acceleration
+#pragma unroll
+        for (int k = 0; k < 8; k++) S.btmp[lane][k] = 0.0f;
       }
-      if (lane == 0) S.c.lcg_seed = lcg_jump(seed0, (uint32_t)__float_as_int(S.aux[8]));
+      if (lane == 0) S.pgs_on = 1;
+    } else if (lane == 0) S.pgs_on = 0;
+    __syncthreads();
 
+    // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
+    if (wid == 0) pgs_packed(sm, cfg.pgs_iters, lane);
+    __syncthreads();
+
+    bool parked_now = false;
+    if (do_part_a) {
+      if (lane == 0) S.c.lcg_seed = lcg_jump(S.c.lcg_seed, (uint32_t)S.n_draws);
       // ------------------------------------------------------------ velocity update + dxStepBody
       if (body_lane) {
+#pragma unroll
+        const float* fc = S.btmp[lane];
 #pragma unroll
         for (int k = 0; k < 3; k++) { lvel[k] += h * fc[k]; avel[k] += h * fc[3 + k]; }
         const float hm = h * invMass;
@@ -700,7 +760,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
             if (c.has_last_state) {
               if (c.pending_valid) append_transition(P, c, env_global, false, 0.0f);
               for (int i = 0; i < 17; i++) c.pending[i] = c.last_state[i];
-              c.pending[17] = (float)c.steering_rate; c.pending[18] = (float)c.boggie_torque; c.pending[19] = (float)reward;
+              c.pending[17] = (float)c.steering_rate; c.pending[18] = (float)c.boggie_torque; c.pending[19] = (float)reward; c.pending_reward = reward;
               for (int i = 0; i < 17; i++) c.pending[20 + i] = cur[i];
               c.pending_valid = 1;
             }
@@ -734,8 +794,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         } else c.ic_tick = 0;
       }
       __syncwarp();
-      if (S.c.parked == 1) break;  // hand the env to the policy kernel; part B runs in the next launch
-    } else {
+
+      parked_now = S.c.parked == 1;  // hand the env to the policy kernel; part B runs in the next launch
+    } else if (runnable) {
       // resumed after the policy kernel: TF_model::infer outputs are in policy_act (src/rover_1_tf.cc:184-185)
       if (lane == 0) {
         S.c.steering_rate = (double)S.c.policy_act[0] * 15.0;
@@ -743,8 +804,10 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
         S.c.parked = 0;
       }
       __syncwarp();
+
     }
 
+    if (runnable && !parked_now) {
     // ---------------------------------------------------------------- Rover_1::next_step, second half (src/rover_1.cc:496-502)
     if (lane == 0) {
       Ctrl& c = S.c;
@@ -816,6 +879,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       S.aux[4] = __int_as_float(reason);
     }
     __syncwarp();
+
     budget--;
     if (__float_as_int(S.aux[4]) != 0 && cfg.auto_reset) {
       const uint32_t ep = S.c.episode + 1;
@@ -827,10 +891,13 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
       joint_readouts(S, lane);
       __syncwarp();
     }
+
+    }
   }
 
   // ---------------------------------------------------------------- store the record
   __syncwarp();
+  if (!valid) return;
   if (lane == 0) P.budget[env] = budget;
   {
     EnvRec* st = reinterpret_cast<EnvRec*>(&S.rowJ[0][0]);
@@ -850,6 +917,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) step_kernel(const StepPara
     for (int i = lane; i < N4; i += 32) dst[i] = src[i];
   }
 }
+
 
 // ------------------------------------------------------------------------------------------------
 // reset kernel: construction of env records (initial create, tfode_batch_reset)

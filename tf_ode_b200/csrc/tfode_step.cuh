@@ -31,15 +31,18 @@ struct __align__(16) WarpSm {
   float bR[NB][12];
   float bvel[NB][8];
   float binvI[NB][8];   // xx xy xz yy yz zz invMass -
-  float btmp[NB][8];    // v/h + invM*f
+  float btmp[NB][8];    // v/h + invM*f while the right-hand sides are formed; then fc, the constraint acceleration
+                        // M^-1 J^T lambda accumulated by the sweeps (6 of 8 used)
   float cont[MAXC][8];  // pos, normal, depth, info bits (b1 | b2<<4 | soft<<8)
   float rowJ[MAXROWS][12];
   float rowS[MAXROWS][8];  // rhs, Ad, Ad*cfm, lo, hi, lambda, hdr, (c during build)
   unsigned char order[MAXROWS + 2];
   int isl_off[NISL + 1], isl_m[NISL + 1], isl_base[NISL + 1];
+  int pgs_on, n_draws, pad_i[2];
   float ftraw[12];
-  float aux[24];
+  float aux[12];
   Ctrl c;
+  float bank_skew[4];   // sizeof % 128 == 16: the same row of neighbouring environments starts 4 banks apart
 };
 static_assert(sizeof(EnvRec) <= sizeof(float) * MAXROWS * 12, "record staging aliases the row array");
 
