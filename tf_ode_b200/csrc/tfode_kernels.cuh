@@ -357,16 +357,31 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
             }
           } else {
             const int s = (pass - 1) * 32 + lane;
+            float c[3] = {0, 0, 0}, cl[3] = {0, 0, 0}; int rng[4] = {0, 0, 0, 0};
+            bool cand = false;
             if (s < NSPHERE) {
               const int w = s / 50, k = s - w * 50;
               gbody = 6 + w; soft = (k == 49);
               const float* bR = S.bR[gbody];
-              float c[3];
               mulRv(c, bR, M.ring[k]);  // dBodyGetRelPointPos of the geom offset (ode/wheel.hh:70-72)
               c[0] += S.bpos[gbody][0]; c[1] += S.bpos[gbody][1]; c[2] += S.bpos[gbody][2];
               if (tkind == T_PLANE) n = col_sphere_plane(c, M.sphere_r, cg);
               else if (tkind == T_BOX) n = col_sphere_box(c, M.sphere_r, tpos, tR, tside, cg);
-              else n = col_sphere_hf(P.hf, c, M.sphere_r, cg);
+              else cand = hf_sphere_range(P.hf, c, M.sphere_r, cl, rng);
+            }
+            if (tkind == T_HF) {  // the warp scans the candidate spheres one at a time, in sphere order
+              unsigned cm = __ballot_sync(FULLMASK, cand);
+              while (cm) {
+                const int src = __ffs(cm) - 1; cm &= cm - 1;
+                float cw_[3], cl_[3]; int rg_[4];
+#pragma unroll
+                for (int k = 0; k < 3; k++) { cw_[k] = __shfl_sync(FULLMASK, c[k], src); cl_[k] = __shfl_sync(FULLMASK, cl[k], src); }
+#pragma unroll
+                for (int k = 0; k < 4; k++) rg_[k] = __shfl_sync(FULLMASK, rng[k], src);
+                const int info = __shfl_sync(FULLMASK, gbody | (tbody << 4) | (soft << 8), src);
+                nc_total += col_sphere_hf_warp(P.hf, cw_, cl_, M.sphere_r, rg_, lane, S.cont, nc_total, maxc, info);
+              }
+              continue;
             }
           }
           if (__any_sync(FULLMASK, n > 0)) {

@@ -300,110 +300,147 @@ __device__ __forceinline__ bool point_vs_hf(const HfParams& hf, const float* pw,
 }
 
 // sphere vs heightfield: local minima of the centre-to-surface distance (faces, convex edges, convex
-// vertices); scan order and tests: DESIGN.md D-HF.
-__device__ int col_sphere_hf(const HfParams& hf, const float* cw, float r, CG* out) {
-  float c[3]; hf_to_local(hf, cw, c);
+// vertices); scan order and tests: DESIGN.md D-HF.  The scan is warp-cooperative: a lane first decides
+// whether its sphere can reach the surface at all (hf_sphere_range, block maxima), then the whole warp
+// works on one candidate sphere at a time -- lane = owner cell for the prism reject, lane = (surviving
+// cell, feature) for the six feature tests -- and emits the first four contacts in the canonical order
+// (cells iz-major; per owner vertex, x-edge, z-edge, diagonal, face0, face1).
+__device__ __forceinline__ bool hf_sphere_range(const HfParams& hf, const float* cw, float r, float* c, int* rng) {
+  hf_to_local(hf, cw, c);
   int ix0 = (int)floorf((c[0] - r) * hf.inv_sx), ix1 = (int)floorf((c[0] + r) * hf.inv_sx);
   int iz0 = (int)floorf((c[2] - r) * hf.inv_sz), iz1 = (int)floorf((c[2] + r) * hf.inv_sz);
   if (ix0 < 0) ix0 = 0;
   if (iz0 < 0) iz0 = 0;
   if (ix1 > hf.ncol - 1) ix1 = hf.ncol - 1;
   if (iz1 > hf.nrow - 1) iz1 = hf.nrow - 1;
-  if (ix0 > ix1 || iz0 > iz1) return 0;
-  {
-    int bx1 = min(ix1 + 1, hf.ncol - 1) >> 3, bz1 = min(iz1 + 1, hf.nrow - 1) >> 3;
-    float zm = -1e30f;
-    for (int bz = iz0 >> 3; bz <= bz1; bz++) for (int bx = ix0 >> 3; bx <= bx1; bx++) zm = fmaxf(zm, __ldg(hf.blockmax + bz * hf.nbx + bx));
-    if (c[1] - r > zm) return 0;
-  }
+  rng[0] = ix0; rng[1] = ix1; rng[2] = iz0; rng[3] = iz1;
+  if (ix0 > ix1 || iz0 > iz1) return false;
+  const int bx1 = min(ix1 + 1, hf.ncol - 1) >> 3, bz1 = min(iz1 + 1, hf.nrow - 1) >> 3;
+  float zm = -1e30f;
+  for (int bz = iz0 >> 3; bz <= bz1; bz++) for (int bx = ix0 >> 3; bx <= bx1; bx++) zm = fmaxf(zm, __ldg(hf.blockmax + bz * hf.nbx + bx));
+  return !(c[1] - r > zm);
+}
+
+// one feature (f = 0 vertex, 1 x-edge, 2 z-edge, 3 diagonal, 4 face0, 5 face1) of owner cell (ix, iz) against
+// the sphere (centre c in the HF frame): unit normal nl (HF frame) and centre distance along it
+__device__ __forceinline__ bool hf_feature(const HfParams& hf, const float* c, float r, int ix, int iz, int f, float* nl, float* dist_out) {
+  const bool hx = ix + 1 <= hf.ncol - 1, hz = iz + 1 <= hf.nrow - 1;
   const float r2 = r * r;
-  int cnt = 0;
-#define HF_EMIT(NL0, NL1, NL2, DIST)                                                          \
-  {                                                                                           \
-    float nw0 = (NL0), nw1 = -(NL2), nw2 = (NL1);                                             \
-    out[cnt].n[0] = nw0; out[cnt].n[1] = nw1; out[cnt].n[2] = nw2;                            \
-    out[cnt].p[0] = cw[0] - nw0 * r; out[cnt].p[1] = cw[1] - nw1 * r; out[cnt].p[2] = cw[2] - nw2 * r; \
-    out[cnt].depth = r - (DIST); cnt++;                                                       \
-    if (cnt >= 4) return cnt;                                                                 \
+  const float x0 = ix * hf.sx, z0 = iz * hf.sz;
+  const float hA = hfH(hf, ix, iz);
+  const float hB = hx ? hfH(hf, ix + 1, iz) : hA, hC = hz ? hfH(hf, ix, iz + 1) : hA, hD = (hx && hz) ? hfH(hf, ix + 1, iz + 1) : hA;
+  const float A[3] = {x0, hA, z0}, B[3] = {x0 + hf.sx, hB, z0}, C[3] = {x0, hC, z0 + hf.sz}, D[3] = {x0 + hf.sx, hD, z0 + hf.sz};
+  if (f == 0) {
+    float d[3] = {c[0] - A[0], c[1] - A[1], c[2] - A[2]};
+    float d2 = dot3(d, d);
+    if (!(d2 < r2 && d2 > 0 && d[1] > 0)) return false;
+    bool ok = true;
+    const int nx[6] = {1, -1, 0, 0, 1, -1}, nz[6] = {0, 0, 1, -1, -1, 1};
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      int jx = ix + nx[k], jz = iz + nz[k];
+      if (jx < 0 || jz < 0 || jx > hf.ncol - 1 || jz > hf.nrow - 1) continue;
+      float u[3] = {nx[k] * hf.sx, hfH(hf, jx, jz) - hA, nz[k] * hf.sz};
+      if (dot3(d, u) > 0) ok = false;
+    }
+    if (!ok) return false;
+    float l = sqrtf(d2);
+    nl[0] = d[0] / l; nl[1] = d[1] / l; nl[2] = d[2] / l; *dist_out = l;
+    return true;
   }
-  for (int iz = iz0; iz <= iz1; iz++) for (int ix = ix0; ix <= ix1; ix++) {
-    const bool hx = ix + 1 <= hf.ncol - 1, hz = iz + 1 <= hf.nrow - 1;
-    const float x0 = ix * hf.sx, z0 = iz * hf.sz;
-    const float hA = hfH(hf, ix, iz);
-    const float hB = hx ? hfH(hf, ix + 1, iz) : hA, hC = hz ? hfH(hf, ix, iz + 1) : hA, hD = (hx && hz) ? hfH(hf, ix + 1, iz + 1) : hA;
-    {
+  if (f <= 3) {
+    const float *P0, *P1, *Q1; float Q2[3]; bool has1, has2;
+    if (f == 1) { if (!hx) return false; P0 = A; P1 = B; Q1 = C; has1 = hz; has2 = iz - 1 >= 0; Q2[0] = x0 + hf.sx; Q2[1] = has2 ? hfH(hf, ix + 1, iz - 1) : 0.0f; Q2[2] = z0 - hf.sz; }
+    else if (f == 2) { if (!hz) return false; P0 = A; P1 = C; Q1 = B; has1 = hx; has2 = ix - 1 >= 0; Q2[0] = x0 - hf.sx; Q2[1] = has2 ? hfH(hf, ix - 1, iz + 1) : 0.0f; Q2[2] = z0 + hf.sz; }
+    else { if (!(hx && hz)) return false; P0 = B; P1 = C; Q1 = A; has1 = true; has2 = true; Q2[0] = D[0]; Q2[1] = D[1]; Q2[2] = D[2]; }
+    float ev[3] = {P1[0] - P0[0], P1[1] - P0[1], P1[2] - P0[2]};
+    float w[3] = {c[0] - P0[0], c[1] - P0[1], c[2] - P0[2]};
+    float ee = dot3(ev, ev);
+    float t = dot3(w, ev) / ee;
+    if (!(t > 0 && t < 1)) return false;
+    float d[3] = {w[0] - t * ev[0], w[1] - t * ev[1], w[2] - t * ev[2]};
+    float d2 = dot3(d, d);
+    if (!(d2 < r2 && d2 > 0 && d[1] > 0)) return false;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      if (!(k == 0 ? has1 : has2)) continue;
+      const float* Q = (k == 0) ? Q1 : Q2;
+      float g[3] = {Q[0] - P0[0], Q[1] - P0[1], Q[2] - P0[2]};
+      float s = dot3(g, ev) / ee;
+      float gp[3] = {g[0] - s * ev[0], g[1] - s * ev[1], g[2] - s * ev[2]};
+      if (dot3(d, gp) > 0) ok = false;
+    }
+    if (!ok) return false;
+    float l = sqrtf(d2);
+    nl[0] = d[0] / l; nl[1] = d[1] / l; nl[2] = d[2] / l; *dist_out = l;
+    return true;
+  }
+  if (!(hx && hz)) return false;
+  float n[3];
+  if (f == 4) { n[0] = -(hB - hA) * hf.sz; n[1] = hf.sx * hf.sz; n[2] = -(hC - hA) * hf.sx; }
+  else { n[0] = -(hD - hC) * hf.sz; n[1] = hf.sx * hf.sz; n[2] = -(hD - hB) * hf.sx; }
+  float il = 1.0f / sqrtf(dot3(n, n)); n[0] *= il; n[1] *= il; n[2] *= il;
+  const float* P0 = (f == 4) ? A : D;
+  float w[3] = {c[0] - P0[0], c[1] - P0[1], c[2] - P0[2]};
+  float dist = dot3(n, w);
+  if (!(dist < r)) return false;
+  float fx = c[0] - n[0] * dist, fz = c[2] - n[2] * dist;
+  float u = (fx - x0) * hf.inv_sx, v = (fz - z0) * hf.inv_sz;
+  bool inside = (f == 4) ? (u > 0 && v > 0 && u + v < 1) : (u < 1 && v < 1 && u + v > 1);
+  if (!inside) return false;
+  nl[0] = n[0]; nl[1] = n[1]; nl[2] = n[2]; *dist_out = dist;
+  return true;
+}
+
+// Warp-cooperative scan of one sphere (all arguments warp-uniform).  Contacts go to cont[slot0 ...] (capacity maxc);
+// returns the number generated (<= 4).
+__device__ int col_sphere_hf_warp(const HfParams& hf, const float* cw, const float* c, float r, const int* rng, int lane,
+                                  float (*cont)[8], int slot0, int maxc, int info) {
+  const int ix0 = rng[0], ix1 = rng[1], iz0 = rng[2], iz1 = rng[3];
+  const int ncx = ix1 - ix0 + 1, ncell = ncx * (iz1 - iz0 + 1);
+  const float r2 = r * r;
+  const unsigned lt = (1u << lane) - 1u;
+  int cnt = 0;
+  for (int base = 0; base < ncell; base += 32) {
+    const int cell = base + lane;
+    bool live = false;
+    if (cell < ncell) {  // conservative reject against the prism that holds every feature this vertex owns
+      const int iz = iz0 + cell / ncx, ix = ix0 + cell % ncx;
+      const bool hx = ix + 1 <= hf.ncol - 1, hz = iz + 1 <= hf.nrow - 1;
+      const float x0 = ix * hf.sx, z0 = iz * hf.sz;
+      const float hA = hfH(hf, ix, iz);
+      const float hB = hx ? hfH(hf, ix + 1, iz) : hA, hC = hz ? hfH(hf, ix, iz + 1) : hA, hD = (hx && hz) ? hfH(hf, ix + 1, iz + 1) : hA;
       float lo = fminf(fminf(hA, hB), fminf(hC, hD)), hi = fmaxf(fmaxf(hA, hB), fmaxf(hC, hD));
       float dx = fmaxf(fmaxf(x0 - c[0], c[0] - (x0 + (hx ? hf.sx : 0.0f))), 0.0f);
       float dz = fmaxf(fmaxf(z0 - c[2], c[2] - (z0 + (hz ? hf.sz : 0.0f))), 0.0f);
       float dy = fmaxf(fmaxf(lo - c[1], c[1] - hi), 0.0f);
-      if (dx * dx + dy * dy + dz * dz >= r2) continue;
+      live = !(dx * dx + dy * dy + dz * dz >= r2);
     }
-    const float A[3] = {x0, hA, z0}, B[3] = {x0 + hf.sx, hB, z0}, C[3] = {x0, hC, z0 + hf.sz}, D[3] = {x0 + hf.sx, hD, z0 + hf.sz};
-    {  // vertex A
-      float d[3] = {c[0] - A[0], c[1] - A[1], c[2] - A[2]};
-      float d2 = dot3(d, d);
-      if (d2 < r2 && d2 > 0 && d[1] > 0) {
-        bool ok = true;
-        const int nx[6] = {1, -1, 0, 0, 1, -1}, nz[6] = {0, 0, 1, -1, -1, 1};
-#pragma unroll
-        for (int k = 0; k < 6; k++) {
-          int jx = ix + nx[k], jz = iz + nz[k];
-          if (jx < 0 || jz < 0 || jx > hf.ncol - 1 || jz > hf.nrow - 1) continue;
-          float u[3] = {nx[k] * hf.sx, hfH(hf, jx, jz) - hA, nz[k] * hf.sz};
-          if (dot3(d, u) > 0) ok = false;
+    const unsigned lm = __ballot_sync(FULLMASK, live);
+    const int nitems = __popc(lm) * 6;
+    for (int i0 = 0; i0 < nitems; i0 += 32) {
+      const int item = i0 + lane;
+      bool hit = false; float nl[3] = {0, 0, 0}, dist = 0;
+      if (item < nitems) {
+        const int k = item / 6, f = item - k * 6;
+        const int cl = base + (int)__fns(lm, 0, k + 1);
+        hit = hf_feature(hf, c, r, ix0 + cl % ncx, iz0 + cl / ncx, f, nl, &dist);
+      }
+      const unsigned hm = __ballot_sync(FULLMASK, hit);
+      if (hit) {
+        const int slot = cnt + __popc(hm & lt);
+        if (slot < 4 && slot0 + slot < maxc) {
+          float* d = cont[slot0 + slot];
+          const float nw0 = nl[0], nw1 = -nl[2], nw2 = nl[1];
+          d[0] = cw[0] - nw0 * r; d[1] = cw[1] - nw1 * r; d[2] = cw[2] - nw2 * r; d[3] = nw0; d[4] = nw1; d[5] = nw2;
+          d[6] = r - dist; d[7] = __int_as_float(info);
         }
-        if (ok) { float l = sqrtf(d2); HF_EMIT(d[0] / l, d[1] / l, d[2] / l, l); }
       }
-    }
-    // edges (P0->P1, third vertices Q1/Q2 of the adjacent faces)
-#pragma unroll 1
-    for (int e = 0; e < 3; e++) {
-      const float *P0, *P1, *Q1; float Q2[3]; bool has1, has2;
-      if (e == 0) { if (!hx) continue; P0 = A; P1 = B; Q1 = C; has1 = hz; has2 = iz - 1 >= 0; Q2[0] = x0 + hf.sx; Q2[1] = has2 ? hfH(hf, ix + 1, iz - 1) : 0.0f; Q2[2] = z0 - hf.sz; }
-      else if (e == 1) { if (!hz) continue; P0 = A; P1 = C; Q1 = B; has1 = hx; has2 = ix - 1 >= 0; Q2[0] = x0 - hf.sx; Q2[1] = has2 ? hfH(hf, ix - 1, iz + 1) : 0.0f; Q2[2] = z0 + hf.sz; }
-      else { if (!(hx && hz)) continue; P0 = B; P1 = C; Q1 = A; has1 = true; has2 = true; Q2[0] = D[0]; Q2[1] = D[1]; Q2[2] = D[2]; }
-      float ev[3] = {P1[0] - P0[0], P1[1] - P0[1], P1[2] - P0[2]};
-      float w[3] = {c[0] - P0[0], c[1] - P0[1], c[2] - P0[2]};
-      float ee = dot3(ev, ev);
-      float t = dot3(w, ev) / ee;
-      if (!(t > 0 && t < 1)) continue;
-      float d[3] = {w[0] - t * ev[0], w[1] - t * ev[1], w[2] - t * ev[2]};
-      float d2 = dot3(d, d);
-      if (!(d2 < r2 && d2 > 0 && d[1] > 0)) continue;
-      bool ok = true;
-#pragma unroll
-      for (int f = 0; f < 2; f++) {
-        if (!(f == 0 ? has1 : has2)) continue;
-        const float* Q = (f == 0) ? Q1 : Q2;
-        float g[3] = {Q[0] - P0[0], Q[1] - P0[1], Q[2] - P0[2]};
-        float s = dot3(g, ev) / ee;
-        float gp[3] = {g[0] - s * ev[0], g[1] - s * ev[1], g[2] - s * ev[2]};
-        if (dot3(d, gp) > 0) ok = false;
-      }
-      if (!ok) continue;
-      float l = sqrtf(d2);
-      HF_EMIT(d[0] / l, d[1] / l, d[2] / l, l);
-    }
-    if (hx && hz) {
-#pragma unroll 1
-      for (int f = 0; f < 2; f++) {
-        float n[3];
-        if (f == 0) { n[0] = -(hB - hA) * hf.sz; n[1] = hf.sx * hf.sz; n[2] = -(hC - hA) * hf.sx; }
-        else { n[0] = -(hD - hC) * hf.sz; n[1] = hf.sx * hf.sz; n[2] = -(hD - hB) * hf.sx; }
-        float il = 1.0f / sqrtf(dot3(n, n)); n[0] *= il; n[1] *= il; n[2] *= il;
-        const float* P0 = (f == 0) ? A : D;
-        float w[3] = {c[0] - P0[0], c[1] - P0[1], c[2] - P0[2]};
-        float dist = dot3(n, w);
-        if (!(dist < r)) continue;
-        float fx = c[0] - n[0] * dist, fz = c[2] - n[2] * dist;
-        float u = (fx - x0) * hf.inv_sx, v = (fz - z0) * hf.inv_sz;
-        bool inside = (f == 0) ? (u > 0 && v > 0 && u + v < 1) : (u < 1 && v < 1 && u + v > 1);
-        if (!inside) continue;
-        HF_EMIT(n[0], n[1], n[2], dist);
-      }
+      cnt += __popc(hm);
+      if (cnt >= 4) return 4;
     }
   }
-#undef HF_EMIT
   return cnt;
 }
 
