@@ -217,6 +217,18 @@ __device__ void pgs_packed(WarpSm* sm, int pgs_iters, int lane) {
   }
 }
 
+// Developer-only phase timers (build with -DTFODE_PHASE_TIMING: tools/phase_timing.py); never compiled into the product library.
+#ifdef TFODE_PHASE_TIMING
+__device__ unsigned long long g_phase_cycles[8];
+#define PT_DECL long long pt_t = clock64(); long long pt_acc[6] = {0, 0, 0, 0, 0, 0};
+#define PT_MARK(i) { long long t_ = clock64(); pt_acc[i] += t_ - pt_t; pt_t = t_; }
+#define PT_FLUSH if (threadIdx.x == 0) { for (int i_ = 0; i_ < 6; i_++) atomicAdd(&g_phase_cycles[i_], (unsigned long long)pt_acc[i_]); }
+#else
+#define PT_DECL
+#define PT_MARK(i)
+#define PT_FLUSH
+#endif
+
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -279,6 +291,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
   float iI[6] = {0, 0, 0, 0, 0, 0};  // world inverse inertia of my body: xx xy xz yy yz zz
 
   // ================================================================== sub-step loop (CTA-uniform trip count)
+  PT_DECL
   for (;;) {
     __syncwarp();
     if (valid && S.c.frozen) budget = 0;
@@ -412,6 +425,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
       if (lane == 0) S.c.n_contacts = nc_total;
       __syncwarp();
 
+      PT_MARK(0)
       // ------------------------------------------------------------ islands: which rover groups touch which step box
       int lab_of_group[NISL];
       {
@@ -674,11 +688,15 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
       }
       if (lane == 0) S.pgs_on = 1;
     } else if (lane == 0) S.pgs_on = 0;
+    PT_MARK(1)
     __syncthreads();
+    PT_MARK(2)
 
     // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
     if (wid == 0) pgs_packed(sm, cfg.pgs_iters, lane);
+    PT_MARK(3)
     __syncthreads();
+    PT_MARK(4)
 
     bool parked_now = false;
     if (do_part_a) {
@@ -916,8 +934,10 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
     }
 
     }
+    PT_MARK(5)
   }
 
+  PT_FLUSH
   // ---------------------------------------------------------------- store the record
   __syncwarp();
   if (!valid) return;

@@ -1,0 +1,37 @@
+"""Developer tool: per-phase cycle split of step_kernel (build with -DTFODE_PHASE_TIMING into a scratch library).
+
+  python tools/phase_timing.py [workload] [envs]      (on the GPU box)
+"""
+import ctypes as C
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+src = os.path.join(ROOT, "tf_ode_b200", "csrc")
+lib = os.path.join(ROOT, "gpurun_out", "libtfode_phase.so")
+os.makedirs(os.path.dirname(lib), exist_ok=True)
+subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-fmad=false", "-DTFODE_PHASE_TIMING",
+                       "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared", "-cudart", "static", "-o", lib, os.path.join(src, "tfode_capi.cu")])
+import tf_ode_b200.engine as eng  # noqa: E402
+eng.LIB_PATH = lib
+import bench  # noqa: E402
+from tf_ode_b200 import RoverBatch, abi, glorot_policy  # noqa: E402
+
+wl = sys.argv[1] if len(sys.argv) > 1 else "config2"
+n = int(sys.argv[2]) if len(sys.argv) > 2 else bench.WORKLOADS[wl][1]
+g = RoverBatch(bench.make_cfg(wl, n))
+if g.cfg.controller == abi.CTRL_MLP:
+    g.load_policy(glorot_policy())
+out = (C.c_ulonglong * 8)()
+g.step(300); g.sync()
+g.L.tfode_debug_phase_cycles(out, 1)
+g.step(300); g.sync()
+g.L.tfode_debug_phase_cycles(out, 0)
+names = ["collide", "rows+rhs+order", "wait(before pgs)", "pgs (warp 0)", "wait(after pgs)", "integrate+robot+control"]
+tot = float(sum(out[:6]))
+ncta = (n + 7) // 8
+for nm, v in zip(names, out[:6]):
+    print("%-26s %5.1f%%   %8.0f cycles per CTA-substep" % (nm, 100 * v / tot, v / ncta / 300))
+print("total %.0f cycles per CTA-substep (%s, %d envs)" % (tot / ncta / 300, wl, n))
