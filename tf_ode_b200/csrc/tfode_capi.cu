@@ -545,8 +545,8 @@ int tfode_batch_set_state(TfodeBatch* b, int env, const TfodeEnvState* s) {
 #ifdef TFODE_PHASE_TIMING
 // developer build only: cumulative cycles per phase (collide, build, wait, pgs, wait, post), summed over CTAs (thread 0's clock)
 int tfode_debug_phase_cycles(unsigned long long* out8, int reset) {
-  if (cudaMemcpyFromSymbol(out8, g_phase_cycles, sizeof(unsigned long long) * 8) != cudaSuccess) return TFODE_ECUDA;
-  if (reset) { unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
+  if (cudaMemcpyFromSymbol(out8, g_phase_cycles, sizeof(unsigned long long) * 16) != cudaSuccess) return TFODE_ECUDA;
+  if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z)); }
   return TFODE_OK;
 }
 #endif

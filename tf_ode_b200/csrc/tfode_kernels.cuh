@@ -171,63 +171,171 @@ __device__ __forceinline__ void pgs_row_update(WarpSm& S, int row, const RowStat
   }
 }
 
-// Sweeps of all environments of the CTA, one lane per island: lane = 4*slot + i; i = 0,1,2 own island labels
-// 0,1,2 (chassis group, front axle, rear axle, each possibly merged with a step box), i = 3 owns labels 3 and 4
-// (the step boxes when nothing touches them).  Every island draws its Fisher-Yates swaps from its own slice of
-// the environment's dRand() stream, exactly as a sequential island-by-island solve would.
-__device__ void pgs_packed(WarpSm* sm, int pgs_iters, int lane) {
-  const int e = lane >> 2, i = lane & 3;
-  WarpSm& S = sm[e];
-  const bool on = e < ENVS_PER_CTA && S.pgs_on != 0;
-  int off = 0, m0 = 0, m1 = 0, base0 = 0, base1 = 0;
-  uint32_t seed0 = 0;
-  if (on) {
-    seed0 = S.c.lcg_seed;
-    off = S.isl_off[i]; m0 = S.isl_m[i]; base0 = S.isl_base[i];
-    if (i == 3) { m1 = S.isl_m[4]; base1 = S.isl_base[4]; }
-  }
-  const int m = m0 + m1;
-  const int maxm = __reduce_max_sync(FULLMASK, m);
-  unsigned char* ord = S.order + off;
-  for (int it = 0; it < pgs_iters; it++) {
-    if ((it & 7) == 0) {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt
-#pragma unroll 1
-      for (int sg = 0; sg < 2; sg++) {
-        const int mm = sg ? m1 : m0;
-        if (mm > 1) {
-          unsigned char* o = ord + (sg ? m0 : 0);
-          uint32_t sd = lcg_jump(seed0, (uint32_t)((sg ? base1 : base0) + (it >> 3) * (mm - 1)));
-          for (int q = 1; q < mm; q++) {
-            const int sw = lcg_randint(sd, (uint32_t)(q + 1));
-            const unsigned char a = o[q], b = o[sw];
-            o[q] = b; o[sw] = a;
-          }
-        }
-      }
-    }
-    int r_cur = (m > 0) ? ord[0] : 0, r_nxt = (m > 1) ? ord[1] : r_cur;
-    RowStatic cur; pgs_load_static(S, r_cur, cur);
-#pragma unroll 1
-    for (int k = 0; k < maxm; k++) {
-      const int r_n2 = (k + 2 < m) ? ord[k + 2] : r_nxt;
-      RowStatic nxt; pgs_load_static(S, r_nxt, nxt);
-      pgs_row_update(S, r_cur, cur, k < m);
-      cur = nxt; r_cur = r_nxt; r_nxt = r_n2;
-    }
-  }
-}
-
 // Developer-only phase timers (build with -DTFODE_PHASE_TIMING: tools/phase_timing.py); never compiled into the product library.
 #ifdef TFODE_PHASE_TIMING
-__device__ unsigned long long g_phase_cycles[8];
+__device__ unsigned long long g_phase_cycles[16];
 #define PT_DECL long long pt_t = clock64(); long long pt_acc[6] = {0, 0, 0, 0, 0, 0};
 #define PT_MARK(i) { long long t_ = clock64(); pt_acc[i] += t_ - pt_t; pt_t = t_; }
 #define PT_FLUSH if (threadIdx.x == 0) { for (int i_ = 0; i_ < 6; i_++) atomicAdd(&g_phase_cycles[i_], (unsigned long long)pt_acc[i_]); }
+#define PG_DECL long long pg_t = clock64();
+#define PG_MARK(i) { long long t_ = clock64(); if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[8 + i], (unsigned long long)(t_ - pg_t)); pg_t = t_; }
 #else
+#define PG_DECL
+#define PG_MARK(i)
 #define PT_DECL
 #define PT_MARK(i)
 #define PT_FLUSH
 #endif
+
+// ------------------------------------------------------------------------------------------------
+// Gauss-Seidel sweeps, "body-lane" form.  A half-warp owns one environment and lane b of it owns rigid body b:
+// the constraint acceleration fc of the body, its world inverse inertia and inverse mass stay in that lane's
+// registers for the whole solve.  A row touches at most two bodies, so its relaxation is carried out by the
+// two lanes of its bodies: each forms its half of J.fc, one shuffle completes the 12-wide dot product, both
+// compute the same delta and each updates its own fc.
+//
+// Order.  ODE relaxes the rows of an island strictly one after the other, in the (randomly permuted) order[]
+// of that island.  Two rows that share no body commute exactly -- neither reads anything the other writes --
+// so the sequential result is reproduced bit for bit when every BODY sees its own rows in the island's order:
+// each lane walks the queue of the rows that touch its body (the sub-sequence of order[] it takes part in)
+// and a row fires as soon as it is at the head of the queues of both of its bodies.  The number of
+// dependent steps per sweep drops from the island's row count to the longest per-body chain, and the
+// islands of an environment (and the two environments of a warp) advance concurrently.
+// ------------------------------------------------------------------------------------------------
+struct BodyRow { int row, pl, flam; bool is1, solo, fric; float J[6]; float a[3]; float rhs, Ad, Adcfm, lo, hi; };
+
+// queue entry = row | is1 << 7 (MAXROWS <= 128): the half of J this body reads is known without the row header
+static_assert(MAXROWS <= 128, "queue entries hold the row index in 7 bits");
+__device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, int hbase, int lane, const float* iI, BodyRow& r) {
+  const int row = entry & 127;
+  r.is1 = (entry & 128) != 0;
+  const float2* Jp = reinterpret_cast<const float2*>(&S.rowJ[row][r.is1 ? 0 : 6]);
+  const float2 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
+  const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);   // rhs Ad Adcfm lo
+  const float2 s1 = *reinterpret_cast<const float2*>(&S.rowS[row][RS_HI + 2]);  // hdr, -
+  r.hi = S.rowS[row][RS_HI];
+  const int hdr = __float_as_int(s1.x);
+  const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
+  r.row = row;
+  r.fric = fidx != 255;
+  r.flam = r.fric ? fidx : row;
+  r.solo = b2 >= NB;
+  r.pl = r.solo ? lane : hbase + (r.is1 ? b2 : b1);
+  r.J[0] = j0.x; r.J[1] = j0.y; r.J[2] = j1.x; r.J[3] = j1.y; r.J[4] = j2.x; r.J[5] = j2.y;
+  r.rhs = s0.x; r.Ad = s0.y; r.Adcfm = s0.z; r.lo = s0.w;
+  // angular part of M^-1 J^T for this body (constant during the sweeps)
+  r.a[0] = tfn::dot3(iI[0], iI[1], iI[2], r.J[3], r.J[4], r.J[5]);
+  r.a[1] = tfn::dot3(iI[1], iI[3], iI[4], r.J[3], r.J[4], r.J[5]);
+  r.a[2] = tfn::dot3(iI[2], iI[4], iI[5], r.J[3], r.J[4], r.J[5]);
+}
+
+__device__ __forceinline__ int first_body_of_group(int g) { return g == 0 ? 0 : (g == 1 ? 4 : (g == 2 ? 5 : (g == 3 ? 10 : 11))); }
+
+constexpr int PGS_WARPS = ENVS_PER_CTA / 2;
+
+__device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
+  const int e = 2 * wid + (lane >> 4), b = lane & 15, hbase = lane & 16;
+  WarpSm& S = sm[e];
+  const bool on = S.pgs_on != 0 && b < NB;
+  int off = 0, m = 0, base = 0; bool leader = false;
+  float fc[6] = {0, 0, 0, 0, 0, 0}, iI[6] = {0, 0, 0, 0, 0, 0}, invM = 0;
+  uint32_t seed0 = 0;
+  if (on) {
+    const int g = body_group(b), L = S.isl_lab[g];
+    off = S.isl_off[L]; m = S.isl_m[L]; base = S.isl_base[L];
+    leader = (b == first_body_of_group(g)) && (L == g);
+    const float4 ia = *reinterpret_cast<const float4*>(&S.binvI[b][0]); const float4 ib = *reinterpret_cast<const float4*>(&S.binvI[b][4]);
+    iI[0] = ia.x; iI[1] = ia.y; iI[2] = ia.z; iI[3] = ia.w; iI[4] = ib.x; iI[5] = ib.y; invM = ib.z;
+    seed0 = S.c.lcg_seed;
+  }
+  unsigned char* const ord = S.order + off;
+  unsigned char* const queue = reinterpret_cast<unsigned char*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
+  PG_DECL
+  // rows per body (does not depend on the permutation) -> start of each body's queue
+  int qn = 0;
+  for (int k = 0; k < m; k++) {
+    const int hdr = __float_as_int(S.rowS[ord[k]][RS_HDR]);
+    if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) qn++;
+  }
+  int incl = qn;
+#pragma unroll
+  for (int d = 1; d < 16; d <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, d, 16); if (b >= d) incl += t; }
+  unsigned char* const myq = queue + (incl - qn);
+
+  PG_MARK(0)
+  for (int it = 0; it < pgs_iters; it++) {
+    if ((it & 7) == 0) {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt, this island's slice of the env's stream
+      PG_MARK(3)
+      if (leader && m > 1) {
+        uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it >> 3) * (m - 1)));
+        for (int q = 1; q < m; q++) {
+          const int sw = lcg_randint(sd, (uint32_t)(q + 1));
+          const unsigned char x = ord[q], y = ord[sw];
+          ord[q] = y; ord[sw] = x;
+        }
+      }
+      __syncwarp();
+      PG_MARK(1)
+      int i = 0;
+      for (int k = 0; k < m; k++) {
+        const int r = ord[k];
+        const int hdr = __float_as_int(S.rowS[r][RS_HDR]);
+        if ((hdr & 15) == b) myq[i++] = (unsigned char)(r | 128); else if (((hdr >> 4) & 15) == b) myq[i++] = (unsigned char)r;
+      }
+      __syncwarp();
+      PG_MARK(2)
+    }
+#ifdef TFODE_PHASE_TIMING
+    if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[7], 1ull);
+#endif
+    int cur = 0;
+    BodyRow rb;
+    rb.row = 0; rb.pl = lane; rb.flam = 0; rb.is1 = false; rb.solo = true; rb.fric = false; rb.rhs = 0; rb.Ad = 0; rb.Adcfm = 0; rb.lo = 0; rb.hi = 0;
+#pragma unroll
+    for (int k = 0; k < 6; k++) rb.J[k] = 0;
+    rb.a[0] = 0; rb.a[1] = 0; rb.a[2] = 0;
+    if (qn > 0) pgs_load_row(S, myq[0], hbase, lane, iI, rb);
+    int ent_next = (qn > 1) ? myq[1] : 0;
+    while (__any_sync(FULLMASK, cur < qn)) {
+#ifdef TFODE_PHASE_TIMING
+      if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[6], 1ull);
+#endif
+      const bool have = cur < qn;
+      const int myrow = have ? rb.row : -1;
+      // loop-carried reads: lambda of the row, lambda of the normal row of a friction row (both lanes read before either writes)
+      const float lam = S.rowS[rb.row][RS_LAM];
+      const float lamf = S.rowS[rb.flam][RS_LAM];
+      const float part = tfn::dot6(rb.J, fc);
+      const int prow = __shfl_sync(FULLMASK, myrow, rb.pl);
+      const float other = __shfl_sync(FULLMASK, part, rb.pl);
+      __syncwarp();
+      const bool ready = have && (rb.solo || prow == myrow);
+      float lo = rb.lo, hi = rb.hi;
+      if (rb.fric) { hi = fabsf(hi * lamf); lo = -hi; }
+      const float sum = rb.solo ? part : (rb.is1 ? part + other : other + part);
+      float delta = tfn::fma(rb.Ad, rb.rhs - sum, -(lam * rb.Adcfm));
+      float nl = lam + delta;
+      if (nl < lo) { delta = lo - lam; nl = lo; }
+      else if (nl > hi) { delta = hi - lam; nl = hi; }
+      if (ready) {
+        if (rb.is1) S.rowS[rb.row][RS_LAM] = nl;
+        const float dm = delta * invM;
+        fc[0] = tfn::fma(dm, rb.J[0], fc[0]); fc[1] = tfn::fma(dm, rb.J[1], fc[1]); fc[2] = tfn::fma(dm, rb.J[2], fc[2]);
+        fc[3] = tfn::fma(delta, rb.a[0], fc[3]); fc[4] = tfn::fma(delta, rb.a[1], fc[4]); fc[5] = tfn::fma(delta, rb.a[2], fc[5]);
+        cur++;
+        if (cur < qn) pgs_load_row(S, ent_next, hbase, lane, iI, rb);
+        if (cur + 1 < qn) ent_next = myq[cur + 1];
+      }
+      __syncwarp();
+    }
+  }
+  PG_MARK(3)
+  if (on) {
+    float* o = S.btmp[b];
+    *reinterpret_cast<float4*>(o) = make_float4(fc[0], fc[1], fc[2], fc[3]);
+    *reinterpret_cast<float2*>(o + 4) = make_float2(fc[4], fc[5]);
+  }
+}
 
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -655,7 +763,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
         for (int L = 0; L < NISL; L++) { mL[L] = cntN[L] + cntF[L]; offL[L] = acc; acc += mL[L]; baseL[L] = draws; draws += nshuf * max(mL[L] - 1, 0); }
         if (lane == 0) { S.n_draws = draws; S.c.n_rows = m_total; }
 #pragma unroll
-        for (int L = 0; L < NISL; L++) if (lane == L) { S.isl_off[L] = offL[L]; S.isl_m[L] = mL[L]; S.isl_base[L] = baseL[L]; }
+        for (int L = 0; L < NISL; L++) if (lane == L) { S.isl_off[L] = offL[L]; S.isl_m[L] = mL[L]; S.isl_base[L] = baseL[L]; S.isl_lab[L] = lab_of_group[L]; }
       }
       {
         int pN[NISL], pF[NISL];
@@ -693,7 +801,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
     PT_MARK(2)
 
     // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
-    if (wid == 0) pgs_packed(sm, cfg.pgs_iters, lane);
+    if (wid < PGS_WARPS) pgs_bodylane(sm, cfg.pgs_iters, wid, lane);
     PT_MARK(3)
     __syncthreads();
     PT_MARK(4)

@@ -38,7 +38,8 @@ struct __align__(16) WarpSm {
   float rowS[MAXROWS][8];  // rhs, Ad, Ad*cfm, lo, hi, lambda, hdr, (c during build)
   unsigned char order[MAXROWS + 2];
   int isl_off[NISL + 1], isl_m[NISL + 1], isl_base[NISL + 1];
-  int pgs_on, n_draws, pad_i[2];
+  int isl_lab[NISL + 1];  // island label of each base group (a group merged with a step box takes the smallest group index)
+  int pgs_on, n_draws;
   float ftraw[12];
   float aux[12];
   Ctrl c;

@@ -24,7 +24,7 @@ n = int(sys.argv[2]) if len(sys.argv) > 2 else bench.WORKLOADS[wl][1]
 g = RoverBatch(bench.make_cfg(wl, n))
 if g.cfg.controller == abi.CTRL_MLP:
     g.load_policy(glorot_policy())
-out = (C.c_ulonglong * 8)()
+out = (C.c_ulonglong * 16)()
 g.step(300); g.sync()
 g.L.tfode_debug_phase_cycles(out, 1)
 g.step(300); g.sync()
@@ -34,4 +34,7 @@ tot = float(sum(out[:6]))
 ncta = (n + 7) // 8
 for nm, v in zip(names, out[:6]):
     print("%-26s %5.1f%%   %8.0f cycles per CTA-substep" % (nm, 100 * v / tot, v / ncta / 300))
+print("pgs: %.1f lock-steps per sweep (warp 0 of each CTA), %d sweeps" % (out[6] / max(out[7], 1), out[7]))
+for nm, v in zip(["pgs: queue sizes", "pgs: Fisher-Yates", "pgs: queue fill", "pgs: sweeps"], out[8:12]):
+    print("  %-24s %8.0f cycles per CTA-substep" % (nm, v / ncta / 300))
 print("total %.0f cycles per CTA-substep (%s, %d envs)" % (tot / ncta / 300, wl, n))
