@@ -251,6 +251,9 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   unsigned char* const ord = S.order + off;
   unsigned char* const queue = reinterpret_cast<unsigned char*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
   PG_DECL
+#ifdef TFODE_PHASE_TIMING
+  long long qa[3] = {0, 0, 0}; int nsteps = 0;
+#endif
   // rows per body (does not depend on the permutation) -> start of each body's queue
   int qn = 0;
   for (int k = 0; k < m; k++) {
@@ -298,7 +301,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     int ent_next = (qn > 1) ? myq[1] : 0;
     while (__any_sync(FULLMASK, cur < qn)) {
 #ifdef TFODE_PHASE_TIMING
-      if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[6], 1ull);
+      nsteps++;
+      long long q0 = clock64();
 #endif
       const bool have = cur < qn;
       const int myrow = have ? rb.row : -1;
@@ -309,6 +313,9 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       const int prow = __shfl_sync(FULLMASK, myrow, rb.pl);
       const float other = __shfl_sync(FULLMASK, part, rb.pl);
       __syncwarp();
+#ifdef TFODE_PHASE_TIMING
+      long long q1 = clock64(); qa[0] += q1 - q0;
+#endif
       const bool ready = have && (rb.solo || prow == myrow);
       float lo = rb.lo, hi = rb.hi;
       if (rb.fric) { hi = fabsf(hi * lamf); lo = -hi; }
@@ -317,6 +324,9 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       float nl = lam + delta;
       if (nl < lo) { delta = lo - lam; nl = lo; }
       else if (nl > hi) { delta = hi - lam; nl = hi; }
+#ifdef TFODE_PHASE_TIMING
+      long long q2 = clock64(); qa[1] += q2 - q1;
+#endif
       if (ready) {
         if (rb.is1) S.rowS[rb.row][RS_LAM] = nl;
         const float dm = delta * invM;
@@ -327,8 +337,14 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         if (cur + 1 < qn) ent_next = myq[cur + 1];
       }
       __syncwarp();
+#ifdef TFODE_PHASE_TIMING
+      qa[2] += clock64() - q2;
+#endif
     }
   }
+#ifdef TFODE_PHASE_TIMING
+  if (threadIdx.x == 0) { atomicAdd(&g_phase_cycles[6], (unsigned long long)nsteps); for (int i_ = 0; i_ < 3; i_++) atomicAdd(&g_phase_cycles[12 + i_], (unsigned long long)qa[i_]); }
+#endif
   PG_MARK(3)
   if (on) {
     float* o = S.btmp[b];

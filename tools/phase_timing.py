@@ -12,7 +12,7 @@ sys.path.insert(0, ROOT)
 src = os.path.join(ROOT, "tf_ode_b200", "csrc")
 lib = os.path.join(ROOT, "gpurun_out", "libtfode_phase.so")
 os.makedirs(os.path.dirname(lib), exist_ok=True)
-subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-fmad=false", "-DTFODE_PHASE_TIMING",
+subprocess.check_call(["/usr/local/cuda/bin/nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-fmad=false", "-DTFODE_PHASE_TIMING", *os.environ.get("TFODE_EXTRA", "").split(),
                        "-Xcompiler", "-fPIC", "-Xcompiler", "-ffp-contract=off", "-shared", "-cudart", "static", "-o", lib, os.path.join(src, "tfode_capi.cu")])
 import tf_ode_b200.engine as eng  # noqa: E402
 eng.LIB_PATH = lib
@@ -37,4 +37,5 @@ for nm, v in zip(names, out[:6]):
 print("pgs: %.1f lock-steps per sweep (warp 0 of each CTA), %d sweeps" % (out[6] / max(out[7], 1), out[7]))
 for nm, v in zip(["pgs: queue sizes", "pgs: Fisher-Yates", "pgs: queue fill", "pgs: sweeps"], out[8:12]):
     print("  %-24s %8.0f cycles per CTA-substep" % (nm, v / ncta / 300))
+print("  per lock-step: top->shfl %.0f, delta %.0f, fire+reload %.0f cycles" % tuple(out[12 + i] / max(out[6], 1) for i in range(3)))
 print("total %.0f cycles per CTA-substep (%s, %d envs)" % (tot / ncta / 300, wl, n))
