@@ -222,6 +222,13 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         kern_ms = tot_ms / args.steps
+        traffic = None  # DRAM bytes per launch of the committed ncu capture (same workload, same envs/sub-steps per launch)
+        try:
+            t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json"))).get(args.workload)
+            if t and t["envs"] == n_envs and t["substeps"] == SUBSTEPS:
+                traffic = t["dram_bytes_per_launch"]
+        except Exception:
+            pass
         achieved = ALGO_BYTES_PER_ENV_STEP * n_envs * SUBSTEPS / (kern_ms * 1e-3) / 1e9
         line = {
             "metric": "rover env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -230,7 +237,7 @@ def main():
                        "pgs_iters": cfg.pgs_iters, "dt": 0.001, "sharding": "contiguous env ranges, no data-path collective",
                        "l2": "256 MiB fill between timed steps, outside the per-step CUDA-event pairs"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+                         "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write)", "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                          "kernel": "tfode::step_kernel", "kernel_ms": kern_ms,
                          "note": "algorithmic bytes = 1680 B per env-step (SURVEY 8(d)); the path is FP32-issue/latency bound (sequential PGS), see DESIGN.md"},
             "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(act.nbytes) * world,
