@@ -40,7 +40,7 @@ def make_cfg(workload, n_envs, env_id_offset=0, device=0):
         hm = synthetic_heightmap("rock_groove")
         return make_config(abi.PRESET_MT_RANDOM, n_envs, heightfield=(hm, 3.0, 3.0, (1.0, 0.0, -0.3)), **kw)
     if workload == "config3":
-        return make_config(abi.PRESET_TRAINING, n_envs, **kw)
+        return make_config(abi.PRESET_TRAINING, n_envs, policy_precision=abi.POLICY_TC, **kw)  # actor on tcgen05 (the CPU arm runs it in fp64)
     if workload == "config4":
         return make_config(abi.PRESET_CRAWLING, n_envs, crawler_amp=25.0, crawler_amp_jitter=5.0, crawler_rate_jitter=5.0, **kw)
     if workload == "config5":

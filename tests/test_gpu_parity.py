@@ -174,6 +174,72 @@ def test_policy_infer_is_bit_exact_with_oracle_fp32_path():
     g.close(); o.close()
 
 
+def _bf16(a):
+    """Round fp32 to bf16 (nearest even) and back, the rounding __float2bfloat16_rn applies to the MMA operands."""
+    u = np.ascontiguousarray(a, np.float32).view(np.uint32).astype(np.uint64)
+    u = ((u + 0x7FFF + ((u >> 16) & 1)) >> 16) << 16
+    return u.astype(np.uint32).view(np.float32).reshape(np.shape(a))
+
+
+def numpy_mlp_bf16(w, x):
+    """The tensor-core path's arithmetic: bf16 operands, wide accumulation, fp32 bias/ReLU, bf16 hidden activations
+    into layer 2, fp32 output layer (tf_ode_b200/csrc/tfode_policy_tc.cuh)."""
+    H = 512
+    o = 0
+    W1 = w[o:o + 17 * H].reshape(17, H); o += 17 * H
+    b1 = w[o:o + H]; o += H
+    W2 = w[o:o + H * H].reshape(H, H); o += H * H
+    b2 = w[o:o + H]; o += H
+    W3 = w[o:o + H * 2].reshape(H, 2); o += H * 2
+    b3 = w[o:o + 2]
+    h = np.maximum((_bf16(x).astype(np.float64) @ _bf16(W1).astype(np.float64)).astype(np.float32) + b1, 0)
+    h = np.maximum((_bf16(h).astype(np.float64) @ _bf16(W2).astype(np.float64)).astype(np.float32) + b2, 0)
+    return np.tanh(h.astype(np.float64) @ W3 + b3)
+
+
+@pytest.mark.parametrize("m", [1, 7, 128, 129, 1000, 16384])
+def test_policy_tc_matches_bf16_reference(m):
+    """tcgen05 kernel vs numpy with the same operand rounding: only the fp32 accumulation order differs (<= 2e-4);
+    vs the fp64 MLP on unrounded weights the bf16 operands cost <= 3e-2 on a tanh output (stated tolerance of the
+    TFODE_POLICY_TC path; the fp32 kernel stays the bit-exact parity path)."""
+    g = RoverBatch(make_config(abi.PRESET_TRAINING, 8, policy_precision=abi.POLICY_TC))
+    w = glorot_policy()
+    rs = np.random.RandomState(1)
+    w[17 * 512:17 * 512 + 512] = rs.randn(512).astype(np.float32) * 0.1
+    o2 = 17 * 512 + 512 + 512 * 512
+    w[o2:o2 + 512] = rs.randn(512).astype(np.float32) * 0.1
+    w[-2:] = (0.05, -0.03)
+    g.load_policy(w)
+    x = (np.random.RandomState(m).rand(m, 17).astype(np.float32) * 2 - 1)
+    yd = torch.full((m, 2), 7.0, device="cuda")
+    g.policy_infer(torch.from_numpy(x).cuda(), yd)
+    torch.cuda.synchronize()
+    y = yd.cpu().numpy()
+    assert np.abs(y - numpy_mlp_bf16(w, x)).max() <= 2e-4
+    assert np.abs(y - numpy_mlp(w, x)).max() <= 3e-2
+    g.close()
+
+
+def test_policy_tc_rollout_tracks_fp32_rollout():
+    """rover_training_1 batch with the tensor-core actor inside the step loop (parked list -> policy_tc_kernel ->
+    policy_act in the record): contact counts and the actions applied stay close to the fp32-actor batch over the
+    first policy ticks (the trajectories are chaotic afterwards; statistics are compared, not states)."""
+    n = 256
+    mk = lambda prec: make_config(abi.PRESET_TRAINING, n, policy_precision=prec, exploration=0)  # noqa: E731
+    ga, gb = RoverBatch(mk(abi.POLICY_TC)), RoverBatch(mk(abi.POLICY_FP32))
+    w = glorot_policy()
+    ga.load_policy(w); gb.load_policy(w)
+    ga.step(1450); gb.step(1450)   # IC starts at 1..1.25 s, period 0.5 s: every env has taken exactly one policy action
+    sa = [ga.get_state(e) for e in range(0, n, 17)]
+    sb = [gb.get_state(e) for e in range(0, n, 17)]
+    da = np.array([[s.steering_rate, s.boggie_torque] for s in sa])
+    db = np.array([[s.steering_rate, s.boggie_torque] for s in sb])
+    assert np.all(np.isfinite(da))
+    assert np.abs(da[:, 0] - db[:, 0]).max() <= 15 * 3e-2 and np.abs(da[:, 1] - db[:, 1]).max() <= 25 * 3e-2
+    assert np.abs(da).max() > 1e-3  # the actor really drove the setpoints
+    ga.close(); gb.close()
+
+
 # ----------------------------------------------------------------------------------------------------------------------
 # 4. experience tuples and episode rules (src/rover_1_tf.cc:111-199, src/rover_training_1.cc:212-224)
 # ----------------------------------------------------------------------------------------------------------------------
