@@ -202,25 +202,28 @@ __device__ unsigned long long g_phase_cycles[16];
 // dependent steps per sweep drops from the island's row count to the longest per-body chain, and the
 // islands of an environment (and the two environments of a warp) advance concurrently.
 // ------------------------------------------------------------------------------------------------
-struct BodyRow { int row, pl, flam; bool is1, solo, fric; float J[6]; float a[3]; float rhs, Ad, Adcfm, lo, hi; };
-
-// queue entry = row | is1 << 7 (MAXROWS <= 128): the half of J this body reads is known without the row header
+// Queue entry (16 bits, decoded once per reorder instead of once per lock-step):
+//   row | is1 << 7 | partner body << 8 (the lane's own body for a one-body row) | solo << 12 | fo << 13
+// fo = distance back to the normal row of a friction row (contact rows are laid out normal, friction 1, friction 2), 0 otherwise.
+struct BodyRow { int meta; float J[6]; float a[3]; float rhs, Ad, Adcfm, lo, hi; };
+constexpr int BR_IS1 = 1 << 7, BR_SOLO = 1 << 12;
 static_assert(MAXROWS <= 128, "queue entries hold the row index in 7 bits");
-__device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, int hbase, int lane, const float* iI, BodyRow& r) {
-  const int row = entry & 127;
-  r.is1 = (entry & 128) != 0;
-  const float2* Jp = reinterpret_cast<const float2*>(&S.rowJ[row][r.is1 ? 0 : 6]);
-  const float2 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
-  const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);   // rhs Ad Adcfm lo
-  const float2 s1 = *reinterpret_cast<const float2*>(&S.rowS[row][RS_HI + 2]);  // hdr, -
-  r.hi = S.rowS[row][RS_HI];
-  const int hdr = __float_as_int(s1.x);
+__device__ __forceinline__ int pgs_make_entry(int row, int hdr, int b) {
   const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
-  r.row = row;
-  r.fric = fidx != 255;
-  r.flam = r.fric ? fidx : row;
-  r.solo = b2 >= NB;
-  r.pl = r.solo ? lane : hbase + (r.is1 ? b2 : b1);
+  const bool is1 = b1 == b, solo = b2 >= NB;
+  const int pb = solo ? b : (is1 ? b2 : b1), fo = fidx != 255 ? row - fidx : 0;
+  return row | (is1 ? BR_IS1 : 0) | (pb << 8) | (solo ? BR_SOLO : 0) | (fo << 13);
+}
+// static part of a row for this lane's body; lam = the row's lambda as stored right now
+__device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const float* iI, BodyRow& r, float& lam) {
+  const int row = entry & 127;
+  const float2* Jp = reinterpret_cast<const float2*>(&S.rowJ[row][(entry & BR_IS1) ? 0 : 6]);
+  const float2 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
+  const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);       // rhs Ad Adcfm lo
+  const float2 s1 = *reinterpret_cast<const float2*>(&S.rowS[row][RS_HI]);   // hi lambda
+  static_assert(RS_LAM == RS_HI + 1 && (RS_HI % 2) == 0, "hi and lambda travel in one 8-byte load");
+  r.meta = entry;
+  r.hi = s1.x; lam = s1.y;
   r.J[0] = j0.x; r.J[1] = j0.y; r.J[2] = j1.x; r.J[3] = j1.y; r.J[4] = j2.x; r.J[5] = j2.y;
   r.rhs = s0.x; r.Ad = s0.y; r.Adcfm = s0.z; r.lo = s0.w;
   // angular part of M^-1 J^T for this body (constant during the sweeps)
@@ -234,8 +237,14 @@ __device__ __forceinline__ int first_body_of_group(int g) { return g == 0 ? 0 : 
 constexpr int PGS_WARPS = ENVS_PER_CTA / 2;
 
 __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
-  const int e = 2 * wid + (lane >> 4), b = lane & 15, hbase = lane & 16;
-  WarpSm& S = sm[e];
+  const int e = 2 * wid + (lane >> 4), b = lane & 15;
+  int hbase = lane & 16;
+  asm volatile("" : "+r"(hbase));   // (same reason as s_addr below)
+  // The environment's shared-memory address is made opaque: under the 128-register cap ptxas otherwise rematerialises it
+  // from %tid / %cluster_ctaid (two S2R, ~40 cycles each) inside the lock-step loop instead of keeping it in a register.
+  uint32_t s_addr = (uint32_t)__cvta_generic_to_shared(&sm[e]);
+  asm volatile("" : "+r"(s_addr));
+  WarpSm& S = *reinterpret_cast<WarpSm*>(__cvta_shared_to_generic(s_addr));
   const bool on = S.pgs_on != 0 && b < NB;
   int off = 0, m = 0, base = 0; bool leader = false;
   float fc[6] = {0, 0, 0, 0, 0, 0}, iI[6] = {0, 0, 0, 0, 0, 0}, invM = 0;
@@ -249,10 +258,11 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     seed0 = S.c.lcg_seed;
   }
   unsigned char* const ord = S.order + off;
-  unsigned char* const queue = reinterpret_cast<unsigned char*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
+  unsigned short* const queue = reinterpret_cast<unsigned short*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
+  static_assert(2 * MAXROWS * sizeof(unsigned short) <= sizeof(float) * MAXC * 8, "queues alias the contact list");
   PG_DECL
 #ifdef TFODE_PHASE_TIMING
-  long long qa[3] = {0, 0, 0}; int nsteps = 0;
+  int nsteps = 0;
 #endif
   // rows per body (does not depend on the permutation) -> start of each body's queue
   int qn = 0;
@@ -263,7 +273,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   int incl = qn;
 #pragma unroll
   for (int d = 1; d < 16; d <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, d, 16); if (b >= d) incl += t; }
-  unsigned char* const myq = queue + (incl - qn);
+  unsigned short* const myq = queue + (incl - qn);
 
   PG_MARK(0)
   for (int it = 0; it < pgs_iters; it++) {
@@ -283,7 +293,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       for (int k = 0; k < m; k++) {
         const int r = ord[k];
         const int hdr = __float_as_int(S.rowS[r][RS_HDR]);
-        if ((hdr & 15) == b) myq[i++] = (unsigned char)(r | 128); else if (((hdr >> 4) & 15) == b) myq[i++] = (unsigned char)r;
+        if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r, hdr, b);
       }
       __syncwarp();
       PG_MARK(2)
@@ -291,59 +301,60 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
 #ifdef TFODE_PHASE_TIMING
     if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[7], 1ull);
 #endif
+    // Lock-steps.  The kernel is instruction-issue bound here (two sweep warps per scheduler, in-order issue), so the
+    // loop is written for the fewest instructions per lock-step: queue entries are pre-decoded, the environment's
+    // shared-memory address is pinned in a register, and lambda of a row is read and written by ONE lane only (the
+    // lane of the row's first body, which is also the first body of the friction rows of the same contact) and reaches
+    // the partner inside the shuffle round -- no shared-memory ordering between lanes, no __syncwarp.
     int cur = 0;
     BodyRow rb;
-    rb.row = 0; rb.pl = lane; rb.flam = 0; rb.is1 = false; rb.solo = true; rb.fric = false; rb.rhs = 0; rb.Ad = 0; rb.Adcfm = 0; rb.lo = 0; rb.hi = 0;
+    rb.meta = (b << 8) | BR_SOLO; rb.rhs = 0; rb.Ad = 0; rb.Adcfm = 0; rb.lo = 0; rb.hi = 0;
 #pragma unroll
     for (int k = 0; k < 6; k++) rb.J[k] = 0;
     rb.a[0] = 0; rb.a[1] = 0; rb.a[2] = 0;
-    if (qn > 0) pgs_load_row(S, myq[0], hbase, lane, iI, rb);
-    int ent_next = (qn > 1) ? myq[1] : 0;
+    float lam = 0.0f;
+    if (qn > 0) pgs_load_row(S, myq[0], iI, rb, lam);
+    float lamf = S.rowS[(rb.meta & 127) - ((rb.meta >> 13) & 3)][RS_LAM];
+    int ent_next = (qn > 1) ? myq[1] : rb.meta;
     while (__any_sync(FULLMASK, cur < qn)) {
 #ifdef TFODE_PHASE_TIMING
       nsteps++;
-      long long q0 = clock64();
 #endif
       const bool have = cur < qn;
-      const int myrow = have ? rb.row : -1;
-      // loop-carried reads: lambda of the row, lambda of the normal row of a friction row (both lanes read before either writes)
-      const float lam = S.rowS[rb.row][RS_LAM];
-      const float lamf = S.rowS[rb.flam][RS_LAM];
+      const int row = rb.meta & 127, pl = hbase | ((rb.meta >> 8) & 15);
+      const bool is1 = (rb.meta & BR_IS1) != 0, solo = (rb.meta & BR_SOLO) != 0, fric = (rb.meta >> 13) != 0;
+      const int myrow = have ? row : -1;
       const float part = tfn::dot6(rb.J, fc);
-      const int prow = __shfl_sync(FULLMASK, myrow, rb.pl);
-      const float other = __shfl_sync(FULLMASK, part, rb.pl);
-      __syncwarp();
-#ifdef TFODE_PHASE_TIMING
-      long long q1 = clock64(); qa[0] += q1 - q0;
-#endif
-      const bool ready = have && (rb.solo || prow == myrow);
+      const int prow = __shfl_sync(FULLMASK, myrow, pl);
+      const float other = __shfl_sync(FULLMASK, part, pl);
+      const float lam_o = __shfl_sync(FULLMASK, lam, pl);
+      const float lamf_o = __shfl_sync(FULLMASK, lamf, pl);
+      const float lam_c = is1 ? lam : lam_o, lamf_c = is1 ? lamf : lamf_o;
+      const bool ready = have && (solo || prow == myrow);
       float lo = rb.lo, hi = rb.hi;
-      if (rb.fric) { hi = fabsf(hi * lamf); lo = -hi; }
-      const float sum = rb.solo ? part : (rb.is1 ? part + other : other + part);
-      float delta = tfn::fma(rb.Ad, rb.rhs - sum, -(lam * rb.Adcfm));
-      float nl = lam + delta;
-      if (nl < lo) { delta = lo - lam; nl = lo; }
-      else if (nl > hi) { delta = hi - lam; nl = hi; }
-#ifdef TFODE_PHASE_TIMING
-      long long q2 = clock64(); qa[1] += q2 - q1;
-#endif
+      if (fric) { hi = fabsf(hi * lamf_c); lo = -hi; }
+      const float sum = solo ? part : (is1 ? part + other : other + part);
+      float delta = tfn::fma(rb.Ad, rb.rhs - sum, -(lam_c * rb.Adcfm));
+      float nl = lam_c + delta;
+      if (nl < lo) { delta = lo - lam_c; nl = lo; }
+      else if (nl > hi) { delta = hi - lam_c; nl = hi; }
       if (ready) {
-        if (rb.is1) S.rowS[rb.row][RS_LAM] = nl;
+        if (is1) S.rowS[row][RS_LAM] = nl;
         const float dm = delta * invM;
         fc[0] = tfn::fma(dm, rb.J[0], fc[0]); fc[1] = tfn::fma(dm, rb.J[1], fc[1]); fc[2] = tfn::fma(dm, rb.J[2], fc[2]);
         fc[3] = tfn::fma(delta, rb.a[0], fc[3]); fc[4] = tfn::fma(delta, rb.a[1], fc[4]); fc[5] = tfn::fma(delta, rb.a[2], fc[5]);
         cur++;
-        if (cur < qn) pgs_load_row(S, ent_next, hbase, lane, iI, rb);
-        if (cur + 1 < qn) ent_next = myq[cur + 1];
+        if (cur < qn) {
+          pgs_load_row(S, ent_next, iI, rb, lam);
+          lamf = S.rowS[(ent_next & 127) - ((ent_next >> 13) & 3)][RS_LAM];   // after the store above: sees a normal row relaxed just now
+          if (cur + 1 < qn) ent_next = myq[cur + 1];
+        }
       }
-      __syncwarp();
-#ifdef TFODE_PHASE_TIMING
-      qa[2] += clock64() - q2;
-#endif
     }
+    __syncwarp();
   }
 #ifdef TFODE_PHASE_TIMING
-  if (threadIdx.x == 0) { atomicAdd(&g_phase_cycles[6], (unsigned long long)nsteps); for (int i_ = 0; i_ < 3; i_++) atomicAdd(&g_phase_cycles[12 + i_], (unsigned long long)qa[i_]); }
+  if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[6], (unsigned long long)nsteps);
 #endif
   PG_MARK(3)
   if (on) {
