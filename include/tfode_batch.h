@@ -29,6 +29,8 @@ extern "C" {
 #define TFODE_NACT 2         /* steering rate [deg/s], boggie torque [N.m] */
 #define TFODE_MLP_HIDDEN 512 /* scripts/rover_training_1.py:26-35 */
 #define TFODE_TRANSITION_WIDTH 40 /* env_id, s[17], a[2], r, terminal, s'[17], pad */
+#define TFODE_TREE_INPUTS 14       /* Rover_1_mt::GetState(flip=false, full=false), src/rover_1_mt.cc:30-52 */
+#define TFODE_TREE_MAX_FEATURES 119 /* 14 + 14*15/2: Polynomial_model_tree of degree 2 (model_tree.cc:91-123) */
 
 /* ---- error codes ---------------------------------------------------------- */
 enum {
@@ -51,7 +53,8 @@ enum {
   TFODE_CTRL_EXTERNAL = 0, /* src/scene_1.cc: IC off; commands come from tfode_batch_set_actions (keyboard in the reference) */
   TFODE_CTRL_RANDOM = 1,   /* BASELINE config 2/5: U(-15,15) deg/s, U(-25,25) N.m every IC tick */
   TFODE_CTRL_MLP = 2,      /* src/rover_1_tf.cc:111-199 (17-512-512-2 actor, e-greedy optional) */
-  TFODE_CTRL_CRAWLER = 3   /* src/rover_1_crawlers.cc:40-77 */
+  TFODE_CTRL_CRAWLER = 3,  /* src/rover_1_crawlers.cc:40-77 */
+  TFODE_CTRL_MODEL_TREE = 4 /* src/rover_1_mt.cc:72-83 (two linear / polynomial model trees loaded from YAML) */
 };
 
 /* ---- policy arithmetic ----------------------------------------------------- */
@@ -233,6 +236,52 @@ int tfode_batch_sync(TfodeBatch* b);
 /* Batched policy op on its own (TF_model::infer, tf_cpp_binding.cc:70-113):
  * obs_scaled DEVICE [m,17] -> act DEVICE [m,2] (tanh outputs, unscaled). */
 int tfode_policy_infer(TfodeBatch* b, const float* obs_scaled_dev, int m, float* act_dev);
+
+/* ---- model-tree policy (src/rover_mt.hh, scripts/ModelTree/cpp/model_tree.{hh,cc}) -------------- */
+
+/* One node of a flattened tree, in the order Linear_model_tree::_build_tree_recursively visits them
+ * (model_tree.cc:21-45: root id 1, ids handed out depth-first, child 0 before child 1). */
+typedef struct TfodeTreeNode {
+  int32_t id;          /* Node::id */
+  int32_t terminal;    /* Node::terminal */
+  int32_t child[2];    /* indices into the node array, -1 for a terminal node */
+  int32_t param_off;   /* Node::params = params[param_off .. param_off + n_params) */
+  int32_t n_params;
+} TfodeTreeNode;
+
+/* Linear_model_tree<double>(yaml_file_path, oblique) (model_tree.cc:11-45) on YAML text already in memory.
+ * Outputs are malloc'ed (release with tfode_free); errors -> TFODE_EINVAL, message in tfode_last_error(NULL)
+ * (std::runtime_error in the reference, e.g. "Read 3 split parameters for the node 2 instead of the 2 required ..."). */
+int tfode_model_tree_parse(const char* yaml_text, size_t len, int oblique,
+                           TfodeTreeNode** nodes_out, int32_t* n_nodes_out, double** params_out, int32_t* n_params_out);
+
+/* Rover_1_mt ctor (src/rover_1_mt.cc:13-27): install tree 1 (steering rate) and tree 2 (boggie torque).
+ * degree 1 = Linear_model_tree, 2 = Polynomial_model_tree(degree 2, interaction_only); higher degrees -> TFODE_EINVAL.
+ * Every terminal node (and every split of an oblique tree) must hold n_features + 1 parameters, every straight
+ * split a feature index inside the feature vector: what the reference only detects at predict() time
+ * (model_tree.cc:50-51) is rejected here at load time. */
+int tfode_batch_load_model_trees(TfodeBatch* b, const char* yaml_1, size_t len_1, const char* yaml_2, size_t len_2,
+                                 int oblique, int degree, int interaction_only);
+
+/* Rover_1_mt::InferAction (src/rover_1_mt.cc:56-69) on its own, batched:
+ * state DEVICE double [m,14] -> act DEVICE double [m,2] (steering rate, boggie torque, unclamped),
+ * node DEVICE int32 [m,2] (terminal node ids node_1, node_2; may be NULL). */
+int tfode_model_tree_infer(TfodeBatch* b, const double* state_dev, int m, double* act_dev, int32_t* node_dev);
+
+/* Rover_1_mt::node_1 / node_2 of every env after its last IC tick: DEVICE int32 [n,2]. */
+int tfode_batch_get_tree_nodes(TfodeBatch* b, int32_t* out_dev);
+
+/* ---- heightmap images (ode/heightfield.hh:42-59) -------------------------------------------------- */
+
+/* HeightField(env, pos, heightimage_path, z_scale, ...): decode a PNG and build the height array the reference hands to
+ * dGeomHeightfieldDataBuildDouble: heights[row*ncol + col] = first byte of pixel (col,row) * z_scale / 255, row 0 = top
+ * row of the picture.  NOTE the reference ignores its own `int z_scale` argument and hard-codes 0.3
+ * (heightfield.hh:54); pass 0.3 to reproduce it.  Supported: non-interlaced, 8-bit grey / grey+alpha / RGB / RGBA,
+ * 1/2/4/8-bit grey or palette.  *heights_out is malloc'ed (tfode_free).  Unreadable file -> TFODE_EINVAL with the
+ * reference's message "Can't open <path>". */
+int tfode_heightmap_load_png(const char* path, double z_scale, float** heights_out, int32_t* nrow_out, int32_t* ncol_out);
+int tfode_heightmap_decode_png(const void* png_bytes, size_t len, double z_scale, float** heights_out, int32_t* nrow_out, int32_t* ncol_out);
+void tfode_free(void* p);
 
 #ifdef __cplusplus
 }

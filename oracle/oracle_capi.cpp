@@ -101,6 +101,22 @@ void* orc_create(const TfodeBatchConfig* cfg, int precision, int n_threads) {
 }
 void orc_destroy(void* h) { delete static_cast<BatchBase*>(h); }
 int orc_load_policy(void* h, const float* w, size_t n) { auto* b = static_cast<BatchBase*>(h); b->scene.policy.load(w, n); return b->scene.policy.loaded ? 0 : -1; }
+// Model trees from per-id entries (what YAML::LoadFile gives the reference): ids[k], terminal[k], params[off[k] .. off[k]+cnt[k]).
+int orc_load_model_tree(void* h, int which, int n_entries, const int32_t* ids, const int32_t* terminal, const int32_t* off, const int32_t* cnt,
+                        const double* params, int oblique, int degree, int interaction_only) {
+  auto* b = static_cast<BatchBase*>(h);
+  std::map<int, ModelTree::Entry> y;
+  for (int k = 0; k < n_entries; k++) y[ids[k]] = ModelTree::Entry{terminal[k] != 0, std::vector<double>(params + off[k], params + off[k] + cnt[k])};
+  try { b->scene.tree[which & 1].load(y, oblique != 0, (unsigned)degree, interaction_only != 0); } catch (const std::exception&) { return -1; }
+  return 0;
+}
+int orc_model_tree_predict(void* h, int which, const double* x, int n_in, int m, double* y, int32_t* node) {
+  auto* b = static_cast<BatchBase*>(h);
+  try {
+    for (int i = 0; i < m; i++) { int nd = 0; y[i] = b->scene.tree[which & 1].predict(std::vector<double>(x + (size_t)i * n_in, x + (size_t)(i + 1) * n_in), nd); if (node) node[i] = nd; }
+  } catch (const std::exception&) { return -1; }
+  return 0;
+}
 void orc_step(void* h, int n) { static_cast<BatchBase*>(h)->step(n); }
 void orc_get_state(void* h, int env, TfodeEnvState* s) { static_cast<BatchBase*>(h)->get_state(env, s); }
 void orc_set_state(void* h, int env, const TfodeEnvState* s) { static_cast<BatchBase*>(h)->set_state(env, s); }

@@ -19,6 +19,11 @@
 // PARITY UNPINNED for everything that bottoms out in libode (see ode_restated.hpp).
 // =============================================================================
 #pragma once
+#include <map>
+#include <memory>
+#include <stdexcept>
+#include <string>
+
 #include "../include/tfode_batch.h"
 #include "ode_restated.hpp"
 
@@ -93,10 +98,64 @@ struct Policy {
   }
 };
 
+// Model-tree policy (scripts/ModelTree/cpp/model_tree.{hh,cc}), restated with the reference's own node structure.
+// yaml-cpp is absent here, so the constructor's YAML::Node is replaced by a map  node id -> (terminal, params)  that the
+// tests fill from PyYAML (the library that wrote the files, scripts/ModelTree/model_tree.py:514-520).
+struct ModelTree {
+  struct Node { int id; bool terminal = true; std::vector<double> params; std::unique_ptr<Node> children[2]; explicit Node(int i) : id(i) {} };
+  struct Entry { bool terminal; std::vector<double> params; };
+  bool oblique = false; unsigned degree = 1; bool interaction_only = false;
+  std::unique_ptr<Node> root; int node_count = 1;
+  void build(Node& node, const std::map<int, Entry>& y) {  // _build_tree_recursively, model_tree.cc:21-45
+    const Entry& e = y.at(node.id);
+    node.params = e.params;
+    if (e.terminal) return;
+    node.terminal = false;
+    if (!oblique && node.params.size() != 2) throw std::runtime_error("Read " + std::to_string(node.params.size()) + " split parameters for the node " + std::to_string(node.id) + " instead of the 2 required for a straight tree");
+    for (int child : {0, 1}) { node.children[child].reset(new Node(++node_count)); build(*node.children[child], y); }
+  }
+  void load(const std::map<int, Entry>& y, bool oblique_, unsigned degree_, bool io) {
+    oblique = oblique_; degree = degree_; interaction_only = io; node_count = 1; root.reset(new Node(1)); build(*root, y);
+  }
+  static double inner(const std::vector<double>& in, const std::vector<double>& p) {  // std::inner_product(in.begin(), in.end(), p.begin(), p.back())
+    double acc = p.back();
+    for (size_t i = 0; i < in.size(); i++) acc = acc + in[i] * p[i];
+    return acc;
+  }
+  double traverse(const Node& node, const std::vector<double>& input, int& terminal_node_id) const {  // model_tree.cc:47-65
+    if ((node.terminal || oblique) && input.size() != node.params.size() - 1)
+      throw std::runtime_error("The dimension of the input vector does not fit the number of parameters of the node " + std::to_string(node.id));
+    if (node.terminal) { terminal_node_id = node.id; return inner(input, node.params); }
+    bool side;
+    if (oblique) side = inner(input, node.params) >= 0;
+    else side = input[(size_t)node.params[0]] >= node.params[1];
+    return traverse(*node.children[side ? 0 : 1], input, terminal_node_id);
+  }
+  double predict(const std::vector<double>& input, int& terminal_node_id) const {
+    if (degree <= 1) return traverse(*root, input, terminal_node_id);
+    // Polynomial_model_tree::predict, model_tree.cc:91-123
+    std::vector<double> features = input, prev_chunk = input;
+    std::vector<size_t> indices(input.size());
+    for (size_t i = 0; i < indices.size(); i++) indices[i] = i;
+    for (unsigned d = 1; d < degree; ++d) {
+      std::vector<double> new_chunk;
+      for (size_t i = 0; i < input.size() - (interaction_only ? d : 0); ++i) {
+        const size_t next_index = new_chunk.size();
+        for (size_t c = indices[i + (interaction_only ? 1 : 0)]; c < prev_chunk.size(); ++c) new_chunk.push_back(input[i] * prev_chunk[c]);
+        indices[i] = next_index;
+      }
+      features.insert(features.end(), new_chunk.begin(), new_chunk.end());
+      prev_chunk = new_chunk;
+    }
+    return traverse(*root, features, terminal_node_id);
+  }
+};
+
 struct SharedScene {  // shared by all envs of a batch
   TfodeBatchConfig cfg;
   std::vector<float> hf_data;
   Policy policy;
+  ModelTree tree[2];   // Rover_1_mt::_lmt_ptr_1/_2 (src/rover_1_mt.cc:13-27)
 };
 
 template <class T> struct RoverSim {
@@ -130,6 +189,7 @@ template <class T> struct RoverSim {
   std::vector<std::vector<float>> transitions;  // emitted rows of TFODE_TRANSITION_WIDTH
   // Crawler_1
   float cr_amp = 30, cr_rate = 10, cr_span = 45; double cr_dtorque_dt = 30; int cr_phase = 1;
+  int node_1 = 0, node_2 = 0;   // Rover_1_mt::node_1/node_2
   // scene lambda state
   float speed = 0, ic_start = 1; int64_t time_steps = 0; uint32_t episode = 0, tick = 0;
   double step_yaw_deg = 0;
@@ -589,6 +649,13 @@ template <class T> struct RoverSim {
         }
         for (int i = 0; i < 17; i++) last_state[i] = cur[i];
         has_last_state = true;
+      } break;
+      case TFODE_CTRL_MODEL_TREE: {  // Rover_1_mt::_InternalControl / GetState(false, false) / InferAction, src/rover_1_mt.cc:30-83
+        double cur[17]; getState(cur);
+        std::vector<double> state(cur, cur + 11);          // direction, steering, roll, pitch, boggie, front F, front T
+        state.insert(state.end(), cur + 14, cur + 17);     // rear T (i == 2, the rear forces, is skipped unless full)
+        steering_rate = sc->tree[0].predict(state, node_1);
+        boggie_torque = sc->tree[1].predict(state, node_2);
       } break;
       case TFODE_CTRL_CRAWLER: {  // src/rover_1_crawlers.cc:40-77
         switch (cr_phase) {

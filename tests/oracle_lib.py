@@ -27,6 +27,8 @@ def lib():
         L.orc_destroy.argtypes = [C.c_void_p]
         L.orc_load_policy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
         L.orc_step.argtypes = [C.c_void_p, C.c_int]
+        L.orc_load_model_tree.argtypes = [C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_int] * 3
+        L.orc_model_tree_predict.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_get_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.EnvState)]
         L.orc_set_state.argtypes = [C.c_void_p, C.c_int, C.POINTER(abi.EnvState)]
         L.orc_set_actions.argtypes = [C.c_void_p, C.c_void_p]
@@ -80,6 +82,29 @@ class Oracle:
     def load_policy(self, w):
         w = np.ascontiguousarray(w, dtype=np.float32)
         assert self.L.orc_load_policy(self.h, _p(w), w.size) == 0
+
+    def load_model_trees(self, yaml_1, yaml_2, oblique=False, degree=1, interaction_only=False):
+        """YAML text -> PyYAML dict (the library that wrote the reference's tree files) -> per-id entries for the oracle."""
+        import yaml
+        for which, text in enumerate((yaml_1, yaml_2)):
+            d = yaml.safe_load(text)
+            ids, term, off, cnt, par = [], [], [], [], []
+            for k, v in d.items():
+                p = v["model params"] if v["terminal"] else v["split params"]
+                ids.append(int(k)); term.append(int(bool(v["terminal"]))); off.append(len(par)); cnt.append(len(p)); par.extend(float(x) for x in p)
+            a = [np.ascontiguousarray(x, dtype=np.int32) for x in (ids, term, off, cnt)]
+            par = np.ascontiguousarray(par, dtype=np.float64)
+            rc = self.L.orc_load_model_tree(self.h, which, len(ids), _p(a[0]), _p(a[1]), _p(a[2]), _p(a[3]), _p(par), int(oblique), int(degree), int(interaction_only))
+            if rc != 0:
+                raise RuntimeError("oracle: model tree %d rejected" % (which + 1))
+
+    def model_tree_predict(self, which, x):
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        y = np.zeros(x.shape[0], np.float64)
+        node = np.zeros(x.shape[0], np.int32)
+        if self.L.orc_model_tree_predict(self.h, which, _p(x), x.shape[1], x.shape[0], _p(y), _p(node)) != 0:
+            raise RuntimeError("oracle: model tree predict failed (dimension mismatch)")
+        return y, node
 
     def step(self, n=1):
         self.L.orc_step(self.h, n)

@@ -1,0 +1,250 @@
+"""On-disk formats either side of the stepping path: PNG heightmaps and model-tree YAML.
+
+CPU-only: the readers are host code of the C-ABI library (no kernel is launched).  Golden data comes from the reference
+itself (tools/make_golden.py): heightmap levels decoded from its env_data/*.png, trees fitted/saved/evaluated by its own
+scripts/ModelTree/model_tree.py.
+"""
+import os
+import struct
+import zlib
+
+import numpy as np
+import pytest
+
+import oracle_lib
+from tf_ode_b200 import TfodeError, abi, load_heightmap_png, make_config, parse_model_tree, reference_heightmap
+
+yaml = pytest.importorskip("yaml")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+# ---------------------------------------------------------------------------------------------------------------------- PNG
+def _chunk(t, body):
+    return struct.pack(">I", len(body)) + t + body + struct.pack(">I", zlib.crc32(t + body) & 0xFFFFFFFF)
+
+
+def _paeth(a, b, c):
+    p = a + b - c
+    pa, pb, pc = abs(p - a), abs(p - b), abs(p - c)
+    return a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+
+
+def encode_png(rows, width, depth, ctype, filters, palette=None, idat_split=1, interlace=0, height=None):
+    """rows: list of packed scanlines (bytes).  filters: filter type per row (cycled)."""
+    channels = {0: 1, 2: 3, 3: 1, 4: 2, 6: 4}[ctype]
+    bpp = max(1, channels * depth // 8)
+    raw = bytearray()
+    prev = bytes(len(rows[0]))
+    for y, line in enumerate(rows):
+        f = filters[y % len(filters)]
+        out = bytearray(len(line))
+        for i, v in enumerate(line):
+            a = line[i - bpp] if i >= bpp else 0
+            b = prev[i]
+            c = prev[i - bpp] if i >= bpp else 0
+            pred = (0, a, b, (a + b) >> 1, _paeth(a, b, c))[f]
+            out[i] = (v - pred) & 255
+        raw += bytes([f]) + out
+        prev = line
+    z = zlib.compress(bytes(raw), 6)
+    png = b"\x89PNG\r\n\x1a\n" + _chunk(b"IHDR", struct.pack(">IIBBBBB", width, height or len(rows), depth, ctype, 0, 0, interlace))
+    png += _chunk(b"pHYs", struct.pack(">IIB", 2835, 2835, 1))  # an ancillary chunk, like the reference's files carry
+    if palette is not None:
+        png += _chunk(b"PLTE", bytes(palette))
+    step = max(1, (len(z) + idat_split - 1) // idat_split)
+    for k in range(0, len(z), step):
+        png += _chunk(b"IDAT", z[k:k + step])
+    return png + _chunk(b"IEND", b"")
+
+
+def _levels(h=37, w=53, seed=3):
+    rng = np.random.RandomState(seed)
+    yy, xx = np.mgrid[0:h, 0:w]
+    return ((np.sin(xx / 5.0) * 60 + np.cos(yy / 7.0) * 50 + 128 + rng.randint(-8, 9, size=(h, w))).clip(0, 255)).astype(np.uint8)
+
+
+@pytest.mark.parametrize("ctype", [0, 2, 4, 6])
+@pytest.mark.parametrize("filters", [[0], [1], [2], [3], [4], [0, 1, 2, 3, 4]])
+def test_png_8bit_colour_types_and_filters(ctype, filters):
+    lv = _levels()
+    channels = {0: 1, 2: 3, 4: 2, 6: 4}[ctype]
+    rng = np.random.RandomState(5)
+    px = rng.randint(0, 256, size=lv.shape + (channels,)).astype(np.uint8)
+    px[..., 0] = lv   # the reference keeps the first byte of each pixel (ode/heightfield.hh:54)
+    rows = [px[y].tobytes() for y in range(lv.shape[0])]
+    h = load_heightmap_png(encode_png(rows, lv.shape[1], 8, ctype, filters, idat_split=3))
+    assert h.shape == lv.shape and h.dtype == np.float32
+    assert np.array_equal(h, (lv.astype(np.float64) * 0.3 / 255).astype(np.float32))
+
+
+@pytest.mark.parametrize("depth", [1, 2, 4])
+def test_png_low_bit_depth_grey_and_palette(depth):
+    hgt, wid = 11, 29   # width not a multiple of 8/depth: the last byte of a scanline is partly padding
+    rng = np.random.RandomState(depth)
+    idx = rng.randint(0, 1 << depth, size=(hgt, wid))
+    rows = []
+    for y in range(hgt):
+        bits = "".join(format(v, "0%db" % depth) for v in idx[y])
+        bits += "0" * (-len(bits) % 8)
+        rows.append(bytes(int(bits[i:i + 8], 2) for i in range(0, len(bits), 8)))
+    grey = load_heightmap_png(encode_png(rows, wid, depth, 0, [0, 2, 4]))
+    want = (idx * 255 // ((1 << depth) - 1)).astype(np.float64) * 0.3 / 255
+    assert np.array_equal(grey, want.astype(np.float32))
+    pal = rng.randint(0, 256, size=((1 << depth), 3)).astype(np.uint8)
+    got = load_heightmap_png(encode_png(rows, wid, depth, 3, [1, 3], palette=pal.ravel().tolist()))
+    assert np.array_equal(got, (pal[idx, 0].astype(np.float64) * 0.3 / 255).astype(np.float32))
+
+
+def test_png_z_scale_and_file_path(tmp_path):
+    lv = _levels(8, 8)
+    png = encode_png([lv[y].tobytes() for y in range(8)], 8, 8, 0, [4])
+    p = tmp_path / "m.png"
+    p.write_bytes(png)
+    assert np.array_equal(load_heightmap_png(str(p), 1.0), (lv.astype(np.float64) * 1.0 / 255).astype(np.float32))
+
+
+def test_png_errors_are_loud(tmp_path):
+    lv = _levels(8, 8)
+    rows = [lv[y].tobytes() for y in range(8)]
+    good = encode_png(rows, 8, 8, 0, [1])
+    with pytest.raises(TfodeError, match="Can't open"):   # the reference's message, ode/heightfield.hh:48
+        load_heightmap_png(str(tmp_path / "missing.png"))
+    with pytest.raises(TfodeError, match="signature"):
+        load_heightmap_png(b"JFIF" + good[4:])
+    bad = bytearray(good); bad[40] ^= 0x55
+    with pytest.raises(TfodeError, match="CRC|inflate|past the end"):
+        load_heightmap_png(bytes(bad))
+    with pytest.raises(TfodeError, match="truncated|past the end"):
+        load_heightmap_png(good[:-20])
+    with pytest.raises(TfodeError, match="interlaced"):
+        load_heightmap_png(encode_png(rows, 8, 8, 0, [0], interlace=1))
+    with pytest.raises(TfodeError, match="16-bit"):
+        load_heightmap_png(encode_png([r + r for r in rows], 8, 16, 0, [0]))
+    with pytest.raises(TfodeError, match="inflate"):
+        load_heightmap_png(encode_png(rows[:5], 8, 8, 0, [0], height=8))
+
+
+def test_reference_heightmaps_match_the_committed_levels():
+    """The decoder on the reference's own files (only where /root/reference exists) against the PIL-decoded fixture."""
+    root = "/root/reference/env_data"
+    if not os.path.isdir(root):
+        pytest.skip("/root/reference is not on this machine")
+    for kind, shape in (("rock_step", (200, 200)), ("rock_groove", (200, 200)), ("rock_groove_large", (400, 400))):
+        h = load_heightmap_png(os.path.join(root, "heightmap_%s.png" % kind))
+        assert h.shape == shape
+        assert np.array_equal(h, reference_heightmap(kind))
+
+
+def test_committed_heightmap_levels_have_the_reference_statistics():
+    lv = dict(np.load(os.path.join(GOLD, "heightmap_levels.npz")))
+    assert lv["rock_step"].shape == (200, 200) and lv["rock_step"].min() == 0 and lv["rock_step"].max() == 254
+    assert lv["rock_groove"].shape == (200, 200) and lv["rock_groove"].min() == 86 and lv["rock_groove"].max() == 255
+    assert lv["rock_groove_large"].shape == (400, 400) and (lv["rock_groove_large"][0] == 255).all()
+    assert abs(float(reference_heightmap("rock_groove").max()) - 0.3) < 1e-7
+
+
+# ---------------------------------------------------------------------------------------------------------------------- YAML trees
+def _flatten_like_the_loader(d):
+    """Linear_model_tree::_build_tree_recursively (model_tree.cc:21-45) on the PyYAML dict."""
+    nodes, params = [], []
+    count = [1]
+
+    def rec(node_id):
+        e = d[node_id]
+        p = e["model params"] if e["terminal"] else e["split params"]
+        k = len(nodes)
+        nodes.append(dict(id=node_id, terminal=bool(e["terminal"]), child=[-1, -1], param_off=len(params), n_params=len(p)))
+        params.extend(float(x) for x in p)
+        if not e["terminal"]:
+            for c in (0, 1):
+                count[0] += 1
+                nodes[k]["child"][c] = len(nodes)
+                rec(count[0])
+    rec(1)
+    return nodes, np.array(params)
+
+
+@pytest.mark.parametrize("name", ["1", "2", "poly2"])
+def test_yaml_parser_matches_pyyaml_on_the_reference_written_trees(name):
+    text = open(os.path.join(GOLD, "model_tree_%s.yaml" % name)).read()
+    nodes, par = parse_model_tree(text)
+    wn, wp = _flatten_like_the_loader(yaml.safe_load(text))
+    assert len(nodes) == len(wn)
+    for a, b in zip(nodes, wn):
+        assert a["id"] == b["id"] and a["terminal"] == b["terminal"] and list(a["child"]) == b["child"]
+        assert a["param_off"] == b["param_off"] and a["n_params"] == b["n_params"]
+    assert np.array_equal(par, wp)   # strtod and PyYAML's float() agree bit for bit
+
+
+def test_yaml_parser_accepts_flow_style_quotes_and_comments():
+    d = yaml.safe_load(open(os.path.join(GOLD, "model_tree_1.yaml")).read())
+    for style in (True, None):   # all-flow leaves (PyYAML < 5.1 default) and mixed
+        text = "# header comment\n" + yaml.dump(d, default_flow_style=style, sort_keys=False, width=60) if style is None else None
+        if text is None:
+            lines = ["# Straight Model Tree"]
+            for k, v in d.items():
+                key = "model params" if v["terminal"] else "split params"
+                lines += ["%d:   # node" % k, "  'info': \"%s\"" % v["info"], "  terminal: %s" % ("True" if v["terminal"] else "no"),
+                          "  \"%s\": [%s]" % (key, ",\n     ".join(repr(float(x)) for x in v[key]))]
+            text = "\n".join(lines) + "\n"
+        nodes, par = parse_model_tree(text)
+        wn, wp = _flatten_like_the_loader(d)
+        assert [n["id"] for n in nodes] == [n["id"] for n in wn]
+        assert np.array_equal(par, wp)
+
+
+def test_yaml_parser_errors_follow_the_reference():
+    with pytest.raises(TfodeError, match="Read 3 split parameters for the node 1 instead of the 2 required for a straight tree"):
+        parse_model_tree("1:\n  terminal: false\n  split params: [0, 1.0, 2.0]\n")   # model_tree.cc:33-35
+    nodes, par = parse_model_tree("1:\n  terminal: false\n  split params: [0.5, 1.0, 2.0]\n2:\n  terminal: true\n  model params: [1, 2, 3]\n"
+                                  "3:\n  terminal: true\n  model params: [4, 5, 6]\n", oblique=True)
+    assert [n["id"] for n in nodes] == [1, 2, 3] and par.tolist() == [0.5, 1, 2, 1, 2, 3, 4, 5, 6]
+    with pytest.raises(TfodeError, match="node 3"):
+        parse_model_tree("1:\n  terminal: false\n  split params: [0, 1.0]\n2:\n  terminal: true\n  model params: [1, 2]\n")
+    with pytest.raises(TfodeError, match="not a number"):
+        parse_model_tree("1:\n  terminal: true\n  model params: [1, abc]\n")
+    with pytest.raises(TfodeError, match="no 'terminal'"):
+        parse_model_tree("1:\n  model params: [1, 2]\n")
+
+
+# ---------------------------------------------------------------------------------------------------------------------- oracle trees vs the reference's Python
+@pytest.fixture(scope="module")
+def tree_oracle():
+    o = oracle_lib.Oracle(make_config(abi.PRESET_SCENE_1, 1, scene=abi.SCENE_PLANE), "double")
+    yield o
+    o.close()
+
+
+def test_oracle_model_tree_matches_reference_python_predictions(tree_oracle):
+    """model_tree.py's predict() (sklearn dot product) vs the restated C++ traversal: same terminal nodes, values within
+    a few ulp of the summation-order difference."""
+    io = np.load(os.path.join(GOLD, "model_tree_io.npz"))
+    y1 = open(os.path.join(GOLD, "model_tree_1.yaml")).read()
+    y2 = open(os.path.join(GOLD, "model_tree_2.yaml")).read()
+    tree_oracle.load_model_trees(y1, y2)
+    for which, name in ((0, "1"), (1, "2")):
+        y, node = tree_oracle.model_tree_predict(which, io["X"])
+        assert np.array_equal(node, io["node_" + name])
+        assert np.allclose(y, io["y_" + name], rtol=1e-12, atol=1e-12)
+    yp = open(os.path.join(GOLD, "model_tree_poly2.yaml")).read()
+    tree_oracle.load_model_trees(yp, yp, degree=2)
+    y, node = tree_oracle.model_tree_predict(0, io["X"])
+    assert np.array_equal(node, io["node_poly2"])
+    assert np.allclose(y, io["y_poly2"], rtol=1e-10, atol=1e-10)
+    with pytest.raises(RuntimeError):   # model_tree.cc:50-51: 119 features against 15-parameter models
+        tree_oracle.load_model_trees(y1, y2, degree=2)
+        tree_oracle.model_tree_predict(0, io["X"])
+
+
+def test_oracle_interaction_only_features_follow_sklearn_order(tree_oracle):
+    """Polynomial_model_tree(degree 2, interaction_only) builds x_i*x_j (i<j) in PolynomialFeatures' order."""
+    n = 14
+    nf = n + n * (n - 1) // 2
+    w = np.arange(1, nf + 2, dtype=np.float64) / 7.0
+    text = "1:\n  terminal: true\n  model params: [%s]\n" % ", ".join(repr(float(v)) for v in w)
+    tree_oracle.load_model_trees(text, text, degree=2, interaction_only=True)
+    x = np.random.RandomState(1).uniform(-2, 2, size=(16, n))
+    feats = [x] + [x[:, i:i + 1] * x[:, j:j + 1] for i in range(n) for j in range(i + 1, n)]
+    want = np.hstack(feats) @ w[:-1] + w[-1]
+    y, node = tree_oracle.model_tree_predict(0, x)
+    assert (node == 1).all() and np.allclose(y, want, rtol=1e-12)

@@ -15,7 +15,8 @@ TRANSITION_WIDTH = 40
 POLICY_NFLOATS = 17 * 512 + 512 + 512 * 512 + 512 + 512 * 2 + 2  # 272 898, scripts/rover_training_1.py:26-35
 
 SCENE_PLANE, SCENE_STEP_BOXES, SCENE_HEIGHTFIELD = 0, 1, 2
-CTRL_EXTERNAL, CTRL_RANDOM, CTRL_MLP, CTRL_CRAWLER = 0, 1, 2, 3
+CTRL_EXTERNAL, CTRL_RANDOM, CTRL_MLP, CTRL_CRAWLER, CTRL_MODEL_TREE = 0, 1, 2, 3, 4
+TREE_INPUTS, TREE_MAX_FEATURES = 14, 119
 POLICY_FP32, POLICY_TC = 0, 1
 TERM_NONE, TERM_TIMEOUT, TERM_Y_MAX, TERM_X_GOAL, TERM_UPSIDE_DOWN = 0, 1, 2, 3, 4
 PRESET_SCENE_1, PRESET_MT_RANDOM, PRESET_TRAINING, PRESET_CRAWLING = 0, 1, 2, 3
@@ -40,6 +41,10 @@ class BatchConfig(C.Structure):
         ("hf_length", C.c_float), ("hf_width", C.c_float), ("hf_pos", C.c_float * 3),
         ("seed", C.c_uint64), ("max_contacts", C.c_int32), ("transition_capacity", C.c_int32),
     ]
+
+
+class TreeNode(C.Structure):
+    _fields_ = [("id", C.c_int32), ("terminal", C.c_int32), ("child", C.c_int32 * 2), ("param_off", C.c_int32), ("n_params", C.c_int32)]
 
 
 class EnvState(C.Structure):

@@ -7,10 +7,13 @@ Mirrors tfode_batch_config_default() in csrc/tfode_capi.cu (tests check they agr
   PRESET_CRAWLING   src/crawling.cc:19-27,41-66       Crawler_1 on the bare plane
 """
 import ctypes as C
+import os
 
 import numpy as np
 
 from . import abi
+
+PRESET_MT_TREE = 4  # Python-side preset: src/scene_1_mt.cc as shipped (Rover_1_mt with two model trees, step boxes)
 
 
 def make_config(preset, n_envs=1, **kw):
@@ -61,6 +64,11 @@ def make_config(preset, n_envs=1, **kw):
         c.ic_period = 0.5
         c.ic_start = 1.0
         c.x_goal, c.y_max, c.terminate = 1.0, 0.6, 1
+    elif preset == PRESET_MT_TREE:  # src/scene_1_mt.cc:20-35,54-62,72-132
+        c.controller = abi.CTRL_MODEL_TREE
+        c.ic_period = 0.5
+        c.ic_start = 1.0
+        c.x_goal, c.y_max, c.terminate = 1.0, 0.6, 1
     elif preset == abi.PRESET_TRAINING:
         c.controller = abi.CTRL_MLP
         c.ic_period = 0.5
@@ -101,6 +109,21 @@ def set_heightfield(cfg, heights, length=3.0, width=3.0, pos=(0.0, 0.0, 0.0)):
     cfg.hf_heights = h.ctypes.data_as(C.POINTER(C.c_float))
     cfg._keepalive = h
     return h
+
+
+_LEVELS = None
+
+
+def reference_heightmap(kind):
+    """The reference's own terrain: red-channel levels of env_data/heightmap_<kind>.png (committed as
+    tests/golden/heightmap_levels.npz by tools/make_golden.py, since /root/reference does not travel) turned into
+    heights exactly as ode/heightfield.hh:54 does (level * 0.3 / 255 in double), float32 [nrow, ncol], row 0 = top row.
+    kind: 'rock_step' | 'rock_groove' | 'rock_groove_large'."""
+    global _LEVELS
+    if _LEVELS is None:
+        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "heightmap_levels.npz")
+        _LEVELS = dict(np.load(path))
+    return (_LEVELS[kind].astype(np.float64) * 0.3 / 255).astype(np.float32)
 
 
 def synthetic_heightmap(kind, n=200):

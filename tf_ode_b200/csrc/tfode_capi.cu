@@ -8,7 +8,9 @@
 #include <string>
 #include <vector>
 
+#include "tfode_formats.hpp"
 #include "tfode_kernels.cuh"
+#include "tfode_model_tree.cuh"
 #include "tfode_policy_tc.cuh"
 
 using namespace tfode;
@@ -30,6 +32,10 @@ struct TfodeBatch {
   float* weights = nullptr;   // fp32 W1 b1 W2 b2 W3 b3
   PolicyTC tc;                // bf16 operand copies for the tcgen05 path
   bool has_policy = false;
+  // model trees (TFODE_CTRL_MODEL_TREE): flattened nodes + parameter pools of tree 1 / tree 2
+  TfodeTreeNode* tree_nodes[2] = {nullptr, nullptr}; double* tree_params[2] = {nullptr, nullptr};
+  TreeParams TP{};
+  bool has_trees = false;
   // staging for the host round trip
   float* d_obs = nullptr; float* d_rew = nullptr; uint8_t* d_done = nullptr; float* d_act = nullptr;
   float* h_pin = nullptr; size_t h_pin_bytes = 0;
@@ -256,7 +262,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   *out = nullptr;
   if (cfg->abi_version != TFODE_ABI_VERSION) { g_create_error = "abi_version mismatch"; return TFODE_EINVAL; }
   if (cfg->n_envs <= 0) { g_create_error = "n_envs must be positive"; return TFODE_EINVAL; }
-  if (cfg->scene < 0 || cfg->scene > 2 || cfg->controller < 0 || cfg->controller > 3) { g_create_error = "bad scene/controller"; return TFODE_EINVAL; }
+  if (cfg->scene < 0 || cfg->scene > 2 || cfg->controller < 0 || cfg->controller > TFODE_CTRL_MODEL_TREE) { g_create_error = "bad scene/controller"; return TFODE_EINVAL; }
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD && (!cfg->hf_heights || cfg->hf_ncol < 2 || cfg->hf_nrow < 2)) { g_create_error = "heightfield scene without heights"; return TFODE_EINVAL; }
   if (cfg->max_contacts < 1 || cfg->max_contacts > MAXC) { g_create_error = "max_contacts must be in 1..24"; return TFODE_EINVAL; }
   if (!(cfg->dt > 0) || cfg->pgs_iters < 1 || cfg->pgs_iters > 1000) { g_create_error = "bad dt / pgs_iters"; return TFODE_EINVAL; }
@@ -329,6 +335,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
 
 void tfode_batch_destroy(TfodeBatch* b) {
   if (!b) return;
+  for (int t = 0; t < 2; t++) { cudaFree(b->tree_nodes[t]); cudaFree(b->tree_params[t]); }
   cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
   cudaFree(b->n_parked); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
   cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
@@ -404,10 +411,11 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
   if (!b || n_substeps < 0) return TFODE_EINVAL;
   if (n_substeps == 0) return TFODE_OK;
   const int n = b->cfg.n_envs;
-  const bool mlp = b->cfg.controller == TFODE_CTRL_MLP;
+  const bool mlp = b->cfg.controller == TFODE_CTRL_MLP, mtree = b->cfg.controller == TFODE_CTRL_MODEL_TREE;
   if (mlp && !b->has_policy) { b->err = "TFODE_CTRL_MLP needs tfode_batch_load_policy first"; return TFODE_ESTATE; }
+  if (mtree && !b->has_trees) { b->err = "TFODE_CTRL_MODEL_TREE needs tfode_batch_load_model_trees first"; return TFODE_ESTATE; }
   int rounds = 1;
-  if (mlp) {
+  if (mlp || mtree) {
     int period_steps = b->cfg.ic_period > 0 ? (int)std::floor(b->cfg.ic_period / b->cfg.dt) : 1;
     if (period_steps < 1) period_steps = 1;
     rounds = n_substeps / period_steps + 2;
@@ -423,6 +431,13 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
       if (rc != TFODE_OK) return rc;
       zero_int_kernel<<<1, 1, 0, b->stream>>>(b->n_parked);
       b->launches++;
+    }
+    if (mtree) {
+      const int blocks = std::min((n + 127) / 128, 148 * 8);
+      model_tree_kernel<<<blocks, 128, 0, b->stream>>>(b->TP, b->policy_in, b->parked_list, b->n_parked, b->rec, nullptr, 0, nullptr, nullptr);
+      CK(cudaGetLastError());
+      zero_int_kernel<<<1, 1, 0, b->stream>>>(b->n_parked);
+      b->launches += 2;
     }
   }
   return TFODE_OK;
@@ -540,6 +555,99 @@ int tfode_batch_set_state(TfodeBatch* b, int env, const TfodeEnvState* s) {
   CK(cudaMemcpyAsync(b->rec + env, &r, sizeof(EnvRec), cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));
   return TFODE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------ model trees / heightmap images
+void tfode_free(void* p) { std::free(p); }
+
+int tfode_model_tree_parse(const char* yaml_text, size_t len, int oblique, TfodeTreeNode** nodes_out, int32_t* n_nodes_out, double** params_out, int32_t* n_params_out) {
+  if (!yaml_text || !nodes_out || !n_nodes_out || !params_out || !n_params_out) { g_create_error = "null argument"; return TFODE_EINVAL; }
+  try {
+    const tfode_fmt::FlatTree t = tfode_fmt::parse_model_tree(yaml_text, len, oblique != 0);
+    static_assert(sizeof(tfode_fmt::TreeNode) == sizeof(TfodeTreeNode), "TreeNode mirrors TfodeTreeNode");
+    TfodeTreeNode* nd = (TfodeTreeNode*)std::malloc(sizeof(TfodeTreeNode) * std::max<size_t>(1, t.nodes.size()));
+    double* pr = (double*)std::malloc(sizeof(double) * std::max<size_t>(1, t.params.size()));
+    if (!nd || !pr) { std::free(nd); std::free(pr); g_create_error = "out of memory"; return TFODE_ENOMEM; }
+    std::memcpy(nd, t.nodes.data(), sizeof(TfodeTreeNode) * t.nodes.size());
+    std::memcpy(pr, t.params.data(), sizeof(double) * t.params.size());
+    *nodes_out = nd; *n_nodes_out = (int32_t)t.nodes.size(); *params_out = pr; *n_params_out = (int32_t)t.params.size();
+  } catch (const std::exception& e) { g_create_error = e.what(); return TFODE_EINVAL; }
+  return TFODE_OK;
+}
+
+int tfode_batch_load_model_trees(TfodeBatch* b, const char* yaml_1, size_t len_1, const char* yaml_2, size_t len_2, int oblique, int degree, int interaction_only) {
+  if (!b) return TFODE_EINVAL;
+  if (!yaml_1 || !yaml_2) { b->err = "null argument"; return TFODE_EINVAL; }
+  if (degree < 1 || degree > 2) { b->err = "model tree degree must be 1 (Linear_model_tree) or 2 (Polynomial_model_tree)"; return TFODE_EINVAL; }
+  const int nf = tfode_fmt::poly_feature_count(TFODE_TREE_INPUTS, degree, interaction_only != 0);
+  if (nf < TFODE_TREE_INPUTS || nf > TFODE_TREE_MAX_FEATURES) { b->err = "model tree feature count out of range"; return TFODE_EINVAL; }
+  tfode_fmt::FlatTree t[2];
+  try {
+    t[0] = tfode_fmt::parse_model_tree(yaml_1, len_1, oblique != 0);
+    t[1] = tfode_fmt::parse_model_tree(yaml_2, len_2, oblique != 0);
+    for (int k = 0; k < 2; k++)
+      for (const auto& nd : t[k].nodes) {
+        if ((nd.terminal || oblique) && nd.n_params != nf + 1)   // model_tree.cc:50-51, detected at load time here
+          throw std::runtime_error("The dimension of the input vector does not fit the number of parameters of the node " + std::to_string(nd.id));
+        if (!nd.terminal && !oblique) {
+          const double idx = t[k].params[nd.param_off];
+          if (!(idx >= 0) || idx >= nf || idx != std::floor(idx)) throw std::runtime_error("split feature index of node " + std::to_string(nd.id) + " is outside the feature vector");
+        }
+      }
+  } catch (const std::exception& e) { b->err = e.what(); return TFODE_EINVAL; }
+  CK(cudaSetDevice(b->cfg.device));
+  CK(cudaStreamSynchronize(b->stream));
+  for (int k = 0; k < 2; k++) {
+    cudaFree(b->tree_nodes[k]); cudaFree(b->tree_params[k]); b->tree_nodes[k] = nullptr; b->tree_params[k] = nullptr;
+    CK(cudaMalloc(&b->tree_nodes[k], sizeof(TfodeTreeNode) * t[k].nodes.size()));
+    CK(cudaMalloc(&b->tree_params[k], sizeof(double) * t[k].params.size()));
+    CK(cudaMemcpy(b->tree_nodes[k], t[k].nodes.data(), sizeof(TfodeTreeNode) * t[k].nodes.size(), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(b->tree_params[k], t[k].params.data(), sizeof(double) * t[k].params.size(), cudaMemcpyHostToDevice));
+    b->TP.tree[k].nodes = b->tree_nodes[k]; b->TP.tree[k].params = b->tree_params[k]; b->TP.tree[k].n_nodes = (int)t[k].nodes.size();
+  }
+  b->TP.oblique = oblique != 0; b->TP.degree = degree; b->TP.interaction_only = interaction_only != 0; b->TP.n_features = nf;
+  b->has_trees = true;
+  return TFODE_OK;
+}
+
+int tfode_model_tree_infer(TfodeBatch* b, const double* state_dev, int m, double* act_dev, int32_t* node_dev) {
+  if (!b || !state_dev || !act_dev || m < 0) return TFODE_EINVAL;
+  if (!b->has_trees) { b->err = "no model trees loaded"; return TFODE_ESTATE; }
+  if (m == 0) return TFODE_OK;
+  const int blocks = std::min((m + 127) / 128, 148 * 8);
+  model_tree_kernel<<<blocks, 128, 0, b->stream>>>(b->TP, nullptr, nullptr, nullptr, nullptr, state_dev, m, act_dev, node_dev);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_batch_get_tree_nodes(TfodeBatch* b, int32_t* out_dev) {
+  if (!b || !out_dev) return TFODE_EINVAL;
+  const int n = b->cfg.n_envs;
+  tree_nodes_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->rec, n, out_dev);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
+int tfode_heightmap_decode_png(const void* png_bytes, size_t len, double z_scale, float** heights_out, int32_t* nrow_out, int32_t* ncol_out) {
+  if (!png_bytes || !heights_out || !nrow_out || !ncol_out) { g_create_error = "null argument"; return TFODE_EINVAL; }
+  try {
+    std::vector<unsigned char> lv; int nrow = 0, ncol = 0;
+    tfode_fmt::decode_png((const unsigned char*)png_bytes, len, lv, nrow, ncol);
+    float* h = (float*)std::malloc(sizeof(float) * lv.size());
+    if (!h) { g_create_error = "out of memory"; return TFODE_ENOMEM; }
+    for (size_t i = 0; i < lv.size(); i++) h[i] = (float)((double)lv[i] * z_scale / 255);   // ode/heightfield.hh:54 (double), then the engine's fp32
+    *heights_out = h; *nrow_out = nrow; *ncol_out = ncol;
+  } catch (const std::exception& e) { g_create_error = e.what(); return TFODE_EINVAL; }
+  return TFODE_OK;
+}
+
+int tfode_heightmap_load_png(const char* path, double z_scale, float** heights_out, int32_t* nrow_out, int32_t* ncol_out) {
+  if (!path) { g_create_error = "null argument"; return TFODE_EINVAL; }
+  std::vector<unsigned char> buf;
+  try { buf = tfode_fmt::read_file(path); } catch (const std::exception& e) { g_create_error = e.what(); return TFODE_EINVAL; }
+  return tfode_heightmap_decode_png(buf.data(), buf.size(), z_scale, heights_out, nrow_out, ncol_out);
 }
 
 #ifdef TFODE_PHASE_TIMING

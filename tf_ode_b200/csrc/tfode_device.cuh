@@ -49,7 +49,8 @@ struct Ctrl {
   uint32_t lcg_seed, episode, tick;
   int32_t ic_activated, ic_tick, servo_mode_vel, has_last_state, explore, fork_collision, pending_valid;
   int32_t cr_phase, done_call, done_step, term_reason, n_contacts, episodes_done, frozen, parked;
-  int32_t last_ep_steps, n_rows, pad0;
+  int32_t last_ep_steps, n_rows;
+  int32_t tree_nodes;      // Rover_1_mt::node_1 | node_2 << 16 (terminal nodes reached at the last IC tick)
 };
 
 struct __align__(16) EnvRec {
@@ -87,6 +88,10 @@ struct HfParams {
   float sx, sz, inv_sx, inv_sz, length, width, hmax;
   float pos[3];
 };
+
+// Flattened model trees (tfode_formats.hpp), shared by all environments of a GPU.
+struct TreeDev { const TfodeTreeNode* nodes; const double* params; int n_nodes; };
+struct TreeParams { TreeDev tree[2]; int oblique, degree, interaction_only, n_features; };
 
 struct StepParams {
   EnvRec* rec;

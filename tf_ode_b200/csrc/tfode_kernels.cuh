@@ -956,6 +956,16 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
             }
             for (int i = 0; i < 17; i++) c.last_state[i] = cur[i];
             c.has_last_state = 1;
+          } else if (cfg.controller == TFODE_CTRL_MODEL_TREE) {  // Rover_1_mt::_InternalControl, src/rover_1_mt.cc:72-83
+            // GetState(flip = false, full = false) (:30-52): the 17-vector without the rear forces; the two trees are
+            // walked by model_tree_kernel while the environment is parked and write _steering_rate/_boggie_torque.
+            float cur[17]; get_state17(S, cur);
+            float* in = P.policy_in + (size_t)env * 17;
+            for (int i = 0; i < 11; i++) in[i] = cur[i];
+            for (int i = 0; i < 3; i++) in[11 + i] = cur[14 + i];
+            int slot = atomicAdd(P.n_parked, 1);
+            P.parked_list[slot] = env;
+            park = true;
           } else if (cfg.controller == TFODE_CTRL_CRAWLER) {  // src/rover_1_crawlers.cc:40-77
             const double ang = (double)(c.jq_angle[1] * 57.29577951308232f);
             switch (c.cr_phase) {
@@ -975,8 +985,10 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
     } else if (runnable) {
       // resumed after the policy kernel: TF_model::infer outputs are in policy_act (src/rover_1_tf.cc:184-185)
       if (lane == 0) {
-        S.c.steering_rate = (double)S.c.policy_act[0] * 15.0;
-        S.c.boggie_torque = (double)S.c.policy_act[1] * 25.0;
+        if (cfg.controller == TFODE_CTRL_MLP) {
+          S.c.steering_rate = (double)S.c.policy_act[0] * 15.0;
+          S.c.boggie_torque = (double)S.c.policy_act[1] * 25.0;
+        }  // TFODE_CTRL_MODEL_TREE: model_tree_kernel wrote the two commands into the record
         S.c.parked = 0;
       }
       __syncwarp();

@@ -23,6 +23,8 @@ EXPORTS = [
     "tfode_batch_drain_transitions", "tfode_batch_rollout_host", "tfode_batch_get_state",
     "tfode_batch_set_state", "tfode_batch_launch_count", "tfode_batch_n_envs", "tfode_batch_sync",
     "tfode_policy_infer",
+    "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
+    "tfode_heightmap_load_png", "tfode_heightmap_decode_png", "tfode_free",
 ]
 
 
@@ -62,8 +64,56 @@ def load_library():
     L.tfode_batch_n_envs.argtypes = [vp]
     L.tfode_batch_sync.argtypes = [vp]
     L.tfode_policy_infer.argtypes = [vp, vp, i32, vp]
+    L.tfode_model_tree_parse.argtypes = [C.c_char_p, C.c_size_t, i32, C.POINTER(C.POINTER(abi.TreeNode)), C.POINTER(C.c_int32),
+                                         C.POINTER(C.POINTER(C.c_double)), C.POINTER(C.c_int32)]
+    L.tfode_batch_load_model_trees.argtypes = [vp, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, i32, i32, i32]
+    L.tfode_model_tree_infer.argtypes = [vp, vp, i32, vp, vp]
+    L.tfode_batch_get_tree_nodes.argtypes = [vp, vp]
+    L.tfode_heightmap_load_png.argtypes = [C.c_char_p, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.tfode_heightmap_decode_png.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.tfode_free.argtypes = [vp]
+    L.tfode_free.restype = None
     _LIB = L
     return L
+
+
+def parse_model_tree(yaml_text, oblique=False):
+    """Linear_model_tree's constructor (scripts/ModelTree/cpp/model_tree.cc:11-45) on YAML text: the flattened tree as
+    (nodes, params): nodes = list of dicts in the loader's depth-first order, params = float64 pool.  Raises TfodeError with
+    the reference's runtime_error message on malformed trees."""
+    L = load_library()
+    if isinstance(yaml_text, str):
+        yaml_text = yaml_text.encode()
+    nodes, params = C.POINTER(abi.TreeNode)(), C.POINTER(C.c_double)()
+    nn, npar = C.c_int32(0), C.c_int32(0)
+    rc = L.tfode_model_tree_parse(yaml_text, len(yaml_text), int(oblique), C.byref(nodes), C.byref(nn), C.byref(params), C.byref(npar))
+    if rc != 0:
+        raise TfodeError(L.tfode_last_error(None).decode())
+    try:
+        out = [dict(id=nodes[i].id, terminal=bool(nodes[i].terminal), child=(nodes[i].child[0], nodes[i].child[1]),
+                    param_off=nodes[i].param_off, n_params=nodes[i].n_params) for i in range(nn.value)]
+        par = np.array([params[i] for i in range(npar.value)], dtype=np.float64)
+    finally:
+        L.tfode_free(nodes)
+        L.tfode_free(params)
+    return out, par
+
+
+def load_heightmap_png(path_or_bytes, z_scale=0.3):
+    """ode::HeightField's image constructor (ode/heightfield.hh:42-59): PNG -> float32 [nrow, ncol] heights in metres,
+    row 0 = top row of the picture.  The reference hard-codes 0.3/255 whatever z_scale it is given."""
+    L = load_library()
+    h, nr, nc = C.POINTER(C.c_float)(), C.c_int32(0), C.c_int32(0)
+    if isinstance(path_or_bytes, (bytes, bytearray)):
+        rc = L.tfode_heightmap_decode_png(bytes(path_or_bytes), len(path_or_bytes), z_scale, C.byref(h), C.byref(nr), C.byref(nc))
+    else:
+        rc = L.tfode_heightmap_load_png(os.fsencode(path_or_bytes), z_scale, C.byref(h), C.byref(nr), C.byref(nc))
+    if rc != 0:
+        raise TfodeError(L.tfode_last_error(None).decode())
+    try:
+        return np.ctypeslib.as_array(h, shape=(nr.value, nc.value)).copy()
+    finally:
+        L.tfode_free(h)
 
 
 def _hp(a):
@@ -133,6 +183,19 @@ class RoverBatch:
     def load_policy(self, w):
         w = np.ascontiguousarray(w, dtype=np.float32)
         self._ck(self.L.tfode_batch_load_policy(self.h, _hp(w), w.size))
+
+    def load_model_trees(self, yaml_1, yaml_2, oblique=False, degree=1, interaction_only=False):
+        """Rover_1_mt's constructor (src/rover_1_mt.cc:13-27): YAML text of tree 1 (steering rate) and tree 2 (boggie torque)."""
+        y1 = yaml_1.encode() if isinstance(yaml_1, str) else yaml_1
+        y2 = yaml_2.encode() if isinstance(yaml_2, str) else yaml_2
+        self._ck(self.L.tfode_batch_load_model_trees(self.h, y1, len(y1), y2, len(y2), int(oblique), int(degree), int(interaction_only)))
+
+    def model_tree_infer(self, state_dev, act_dev, node_dev=None):
+        """Rover_1_mt::InferAction batched: float64 [m,14] -> float64 [m,2] (+ int32 [m,2] terminal node ids)."""
+        self._ck(self.L.tfode_model_tree_infer(self.h, _dp(state_dev), state_dev.shape[0], _dp(act_dev), _dp(node_dev)))
+
+    def get_tree_nodes(self, out_dev):
+        self._ck(self.L.tfode_batch_get_tree_nodes(self.h, _dp(out_dev)))
 
     def set_actions(self, actions_dev):
         self._ck(self.L.tfode_batch_set_actions(self.h, _dp(actions_dev)))

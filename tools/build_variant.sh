@@ -12,6 +12,6 @@ else
   cp -r $ROOT/include $T/; cp -r $ROOT/tf_ode_b200/csrc $T/tf_ode_b200/
 fi
 /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -fmad=false -Xcompiler -fPIC -Xcompiler -ffp-contract=off \
-  -shared -cudart static ${TFODE_NVCC_EXTRA} -o $ROOT/build/lib$NAME.so $T/tf_ode_b200/csrc/tfode_capi.cu 2>/dev/null
+  -shared -cudart static ${TFODE_NVCC_EXTRA} -o $ROOT/build/lib$NAME.so $T/tf_ode_b200/csrc/tfode_capi.cu -lz 2>/dev/null
 rm -rf $T
 echo "built build/lib$NAME.so"
