@@ -34,17 +34,17 @@ WORKLOADS = {
 
 
 def make_cfg(workload, n_envs, env_id_offset=0, device=0):
-    from tf_ode_b200 import abi, make_config, synthetic_heightmap
+    from tf_ode_b200 import abi, make_config, reference_heightmap
     kw = dict(env_id_offset=env_id_offset, device=device)
     if workload == "config2":
-        hm = synthetic_heightmap("rock_groove")
+        hm = reference_heightmap("rock_groove")  # the reference's env_data/heightmap_rock_groove.png (levels fixture)
         return make_config(abi.PRESET_MT_RANDOM, n_envs, heightfield=(hm, 3.0, 3.0, (1.0, 0.0, -0.3)), **kw)
     if workload == "config3":
         return make_config(abi.PRESET_TRAINING, n_envs, policy_precision=abi.POLICY_TC, **kw)  # actor on tcgen05 (the CPU arm runs it in fp64)
     if workload == "config4":
         return make_config(abi.PRESET_CRAWLING, n_envs, crawler_amp=25.0, crawler_amp_jitter=5.0, crawler_rate_jitter=5.0, **kw)
     if workload == "config5":
-        hm = synthetic_heightmap("rock_groove_large")
+        hm = reference_heightmap("rock_groove_large")
         return make_config(abi.PRESET_MT_RANDOM, n_envs, heightfield=(hm, 6.0, 6.0, (2.0, 0.0, -0.3)), **kw)
     raise SystemExit("unknown workload %r" % workload)
 

@@ -524,7 +524,7 @@ int tfode_batch_get_state(TfodeBatch* b, int env, TfodeEnvState* s) {
   s->step_yaw_deg = c.step_yaw_deg; s->crawler_amp = c.cr_amp; s->crawler_rate = c.cr_rate; s->crawler_dtorque_dt = c.cr_dtorque_dt;
   s->speed = c.speed; s->ic_start = c.ic_start; s->time_steps = c.time_steps; s->lcg_seed = c.lcg_seed; s->episode = c.episode; s->tick = c.tick;
   s->ic_activated = c.ic_activated; s->ic_tick = c.ic_tick; s->servo_mode_vel = c.servo_mode_vel; s->has_last_state = c.has_last_state;
-  s->explore = c.explore; s->fork_collision = c.fork_collision; s->crawler_phase = c.cr_phase; s->done = c.done_call; s->term_reason = c.term_reason;
+  s->explore = c.explore; s->fork_collision = c.fork_collision; s->crawler_phase = c.cr_phase; s->done = c.done_step; s->term_reason = c.term_reason;
   s->n_contacts = c.n_contacts; s->episodes_done = c.episodes_done;
   return TFODE_OK;
 }
@@ -550,7 +550,7 @@ int tfode_batch_set_state(TfodeBatch* b, int env, const TfodeEnvState* s) {
   for (int i = 0; i < 17; i++) c.last_state[i] = (float)s->last_state[i];
   c.speed = s->speed; c.ic_start = s->ic_start; c.time_steps = s->time_steps; c.lcg_seed = s->lcg_seed; c.tick = s->tick;
   c.ic_activated = s->ic_activated; c.ic_tick = s->ic_tick; c.servo_mode_vel = s->servo_mode_vel; c.has_last_state = s->has_last_state;
-  c.explore = s->explore; c.fork_collision = s->fork_collision; c.cr_phase = s->crawler_phase; c.done_call = s->done; c.term_reason = s->term_reason;
+  c.explore = s->explore; c.fork_collision = s->fork_collision; c.cr_phase = s->crawler_phase; c.done_call = s->done; c.done_step = s->done; c.term_reason = s->term_reason;
   c.n_contacts = s->n_contacts; c.episodes_done = s->episodes_done; c.parked = 0; c.frozen = 0;
   CK(cudaMemcpyAsync(b->rec + env, &r, sizeof(EnvRec), cudaMemcpyHostToDevice, b->stream));
   CK(cudaStreamSynchronize(b->stream));

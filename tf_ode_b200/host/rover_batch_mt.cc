@@ -1,11 +1,15 @@
 // rover_1_mt-style rollout driver over the batched engine (the drop-in for src/scene_1_mt.cc's main()).
 //
-//   rover_batch_mt nodisplay [orientation_deg] [policy] [ic_start_offset] [--envs N] [--gpus G] [--steps S] [--scene steps|groove|plane]
+//   rover_batch_mt nodisplay [orientation_deg] [policy] [ic_start_offset] [--envs N] [--gpus G] [--steps S]
+//                  [--scene steps|groove|plane|<heightmap.png>] [--degree D] [--interaction-only]
 //
 // argv[1..4] keep the meaning they have in src/scene_1_mt.cc:25-48,78-84 (display option, step orientation,
-// policy parameter file, IC start offset).  The model-tree policy of Rover_1_mt is a "next" row:
-// `policy` = "random" (default; BASELINE config 2) draws U(-15,15) deg/s and U(-25,25) N.m at every IC tick, or a
-// path to a raw fp32 actor blob (272 898 floats) which selects the Rover_1_tf MLP controller.
+// policy parameter file, IC start offset).  `policy`:
+//   a path prefix P such that P1.yaml and P2.yaml exist -> Rover_1_mt with those two model trees, exactly the
+//       reference's argv[3] (scene_1_mt.cc:25-30; default there "../scripts/tree_params2_");
+//   "random" (default here; BASELINE config 2) -> U(-15,15) deg/s and U(-25,25) N.m at every IC tick;
+//   any other path -> a raw fp32 actor blob (272 898 floats), which selects the Rover_1_tf MLP controller.
+// `--scene file.png` builds the HeightField of scene_1_mt.cc:66 from that image (3 x 3 m at (1,0,-0.3)).
 // Environments are sharded over G GPUs by contiguous ranges, one host thread and one handle per GPU; there is no
 // data-path collective (environments are independent).  Prints the reference's result line for the first
 // environments of rank 0 and the aggregate statistics of all of them.
@@ -36,7 +40,7 @@ struct Result { long n = 0, success = 0, episodes = 0; double sum_x = 0, sum_y =
 
 int main(int argc, char* argv[]) {
   double orientation = 0, ic_offset = 0; std::string policy = "random", scene = "steps";
-  int n_envs = 4096, n_gpus = 1, n_steps = 10000;
+  int n_envs = 4096, n_gpus = 1, n_steps = 10000, degree = 1; bool interaction_only = false;
   std::vector<std::string> pos;
   for (int i = 1; i < argc; i++) {
     std::string a = argv[i];
@@ -45,6 +49,8 @@ int main(int argc, char* argv[]) {
     else if (a == "--gpus") n_gpus = atoi(need("--gpus"));
     else if (a == "--steps") n_steps = atoi(need("--steps"));
     else if (a == "--scene") scene = need("--scene");
+    else if (a == "--degree") degree = atoi(need("--degree"));
+    else if (a == "--interaction-only") interaction_only = true;
     else pos.push_back(a);
   }
   if (pos.size() > 0 && pos[0] != "nodisplay") { fprintf(stderr, "display/capture: unavailable on this box (no graphics stack); running headless\n"); }
@@ -53,7 +59,9 @@ int main(int argc, char* argv[]) {
   if (pos.size() > 3) { char* e; ic_offset = strtod(pos[3].c_str(), &e); if (*e) throw std::runtime_error("Invalide starting offset: " + pos[3]); }
   if (n_envs < 1 || n_gpus < 1 || n_steps < 1) throw std::runtime_error("--envs/--gpus/--steps must be positive");
   std::vector<float> weights;
-  if (policy != "random") {
+  bool trees = false;
+  if (policy != "random") { std::ifstream t1(policy + "1.yaml"), t2(policy + "2.yaml"); trees = (bool)t1 && (bool)t2; }
+  if (policy != "random" && !trees) {
     std::ifstream f(policy, std::ios::binary);
     if (!f) throw std::runtime_error("cannot open actor blob " + policy);
     f.seekg(0, std::ios::end); size_t bytes = (size_t)f.tellg(); f.seekg(0);
@@ -70,7 +78,8 @@ int main(int argc, char* argv[]) {
       if (n <= 0) return;
       ode::Environment env(0.5, n, g);
       std::unique_ptr<robot::Rover_1> robot;
-      if (weights.empty()) { robot.reset(new robot::Rover_1(env, ode::Vector3d(0, 0, 0))); env.config().controller = TFODE_CTRL_RANDOM; }
+      if (trees) robot.reset(new robot::Rover_1_mt(env, ode::Vector3d(0, 0, 0), policy + "1.yaml", policy + "2.yaml", false, (unsigned)degree, interaction_only));
+      else if (weights.empty()) { robot.reset(new robot::Rover_1(env, ode::Vector3d(0, 0, 0))); env.config().controller = TFODE_CTRL_RANDOM; }
       else { auto* r = new robot::Rover_1_tf(env, ode::Vector3d(0, 0, 0), weights.data(), weights.size()); r->SetExploration(false); robot.reset(r); }
       robot->SetCrawlingMode(true); robot->SetCmdPeriod(0.5); robot->DeactivateIC();        // scene_1_mt.cc:31-34
       robot->UseBuiltInSpeedRamp(0.04f, 0.5f); robot->SetICStart((float)(1.0 + ic_offset));  // :72-84
@@ -84,6 +93,8 @@ int main(int argc, char* argv[]) {
       } else if (scene == "groove") {
         hm = groove_map(200);
         field.reset(new ode::HeightField(env, ode::Vector3d(1, 0, -0.3), hm.data(), 200, 200, 3, 3)); field->set_collision_group("ground");
+      } else if (scene.size() > 4 && scene.substr(scene.size() - 4) == ".png") {   // scene_1_mt.cc:66
+        field.reset(new ode::HeightField(env, ode::Vector3d(1, 0, -0.3), scene.c_str(), 0.3, 3, 3)); field->set_collision_group("ground");
       } else if (scene != "plane") throw std::runtime_error("unknown --scene " + scene);
       Sim_loop sim(0.001f);
       auto t0 = std::chrono::steady_clock::now();

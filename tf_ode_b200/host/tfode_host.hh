@@ -21,11 +21,13 @@
 #pragma once
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <functional>
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <cuda_runtime_api.h>
@@ -75,6 +77,7 @@ class Environment {
     int rc = tfode_batch_create(&_cfg, &_batch);
     if (rc != TFODE_OK) throw std::runtime_error(std::string("tfode_batch_create: ") + tfode_last_error(nullptr));
     if (_policy.size()) tfode_host::check(tfode_batch_load_policy(_batch, _policy.data(), _policy.size()), _batch, "tfode_batch_load_policy");
+    if (_has_trees) _load_trees();
     size_t n = (size_t)_cfg.n_envs;
     _h_bodies.resize(n * TFODE_NBODY * 13); _h_obs.resize(n * TFODE_NOBS); _h_rew.resize(n); _h_done.resize(n);
     if (cudaMalloc((void**)&_d_bodies, _h_bodies.size() * sizeof(float)) != cudaSuccess) throw std::runtime_error("cudaMalloc failed");
@@ -103,9 +106,18 @@ class Environment {
     for (int k = 0; k < 3; k++) _cfg.hf_pos[k] = (float)pos[k];
   }
   void _set_policy(const float* w, size_t n) { _policy.assign(w, w + n); if (_batch) tfode_host::check(tfode_batch_load_policy(_batch, w, n), _batch, "tfode_batch_load_policy"); }
+  void _set_model_trees(const std::string& y1, const std::string& y2, bool oblique, unsigned degree, bool interaction_only) {
+    _tree_yaml[0] = y1; _tree_yaml[1] = y2; _tree_oblique = oblique; _tree_degree = (int)degree; _tree_io = interaction_only; _has_trees = true;
+    if (_batch) _load_trees();
+  }
+  void _load_trees() {
+    tfode_host::check(tfode_batch_load_model_trees(_batch, _tree_yaml[0].data(), _tree_yaml[0].size(), _tree_yaml[1].data(), _tree_yaml[1].size(),
+                                                   _tree_oblique, _tree_degree, _tree_io), _batch, "tfode_batch_load_model_trees");
+  }
   int _take_pending() { int p = _pending_steps; _pending_steps = 0; return p; }
 
  private:
+  std::string _tree_yaml[2]; bool _tree_oblique = false, _tree_io = false, _has_trees = false; int _tree_degree = 1;
   void refresh() {
     finalize();
     if (_cache_valid) return;
@@ -184,6 +196,14 @@ class HeightField : public Object {
  public:
   HeightField(Environment& env, const Vector3d& pos, const float* heights, int ncol, int nrow, double length, double width)
       : Object(env, -1) { if (!heights || ncol < 2 || nrow < 2) throw std::runtime_error("HeightField: empty height data"); env._register_heightfield(heights, ncol, nrow, length, width, pos); }
+  // the image constructor (ode/heightfield.hh:42-59): PNG decoded by the engine's own reader; like the reference, the
+  // `int z_scale` argument is ignored and the heights are level * 0.3 / 255; throws "Can't open <path>" like :48
+  HeightField(Environment& env, const Vector3d& pos, const char* heightimage_path, int /*z_scale*/, double length, double width) : Object(env, -1) {
+    float* h = nullptr; int32_t nrow = 0, ncol = 0;
+    if (tfode_heightmap_load_png(heightimage_path, 0.3, &h, &nrow, &ncol) != TFODE_OK) throw std::runtime_error(tfode_last_error(nullptr));
+    env._register_heightfield(h, ncol, nrow, length, width, pos);
+    tfode_free(h);
+  }
 };
 
 // ode/servo.hh:13-88 -- the centre steering hinge; the software limit stop and the P/velocity logic run on the device.
@@ -301,6 +321,40 @@ class Rover_1_tf : public Rover_1 {
     tfode_batch_sync(b);
     cudaMemcpy(out.data(), d, out.size() * sizeof(float), cudaMemcpyDeviceToHost);
     cudaFree(d);
+    return out;
+  }
+};
+
+// src/rover_mt.hh / src/rover_1_mt.cc:13-27: two model trees loaded from YAML files (tree 1 -> steering rate, tree 2 -> boggie torque)
+class Rover_1_mt : public Rover_1 {
+ public:
+  Rover_1_mt(ode::Environment& env, const Vector3d& pose, const std::string yaml_file_path_1, const std::string yaml_file_path_2,
+             bool oblique_trees = false, unsigned int degree = 1, bool interaction_only = false) : Rover_1(env, pose) {
+    env.config().controller = TFODE_CTRL_MODEL_TREE;
+    env._set_model_trees(_slurp(yaml_file_path_1), _slurp(yaml_file_path_2), oblique_trees, degree, interaction_only);
+  }
+  // node_1 / node_2 (terminal nodes reached at the last IC tick) of environment e
+  std::pair<int, int> GetNodes(int e = 0) {
+    TfodeBatch* b = _env->batch();
+    const int n = _env->n_envs();
+    int32_t* d = nullptr;
+    if (cudaMalloc((void**)&d, (size_t)n * 2 * sizeof(int32_t)) != cudaSuccess) throw std::runtime_error("cudaMalloc failed");
+    int rc = tfode_batch_get_tree_nodes(b, d);
+    if (rc != TFODE_OK) { cudaFree(d); tfode_host::check(rc, b, "tfode_batch_get_tree_nodes"); }
+    tfode_batch_sync(b);
+    int32_t v[2] = {0, 0};
+    cudaMemcpy(v, d + (size_t)e * 2, sizeof(v), cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    return {v[0], v[1]};
+  }
+
+ private:
+  static std::string _slurp(const std::string& path) {
+    FILE* f = std::fopen(path.c_str(), "rb");
+    if (!f) throw std::runtime_error("bad file: " + path);   // YAML::BadFile from YAML::LoadFile (model_tree.cc:15)
+    std::string out; char buf[65536]; size_t k;
+    while ((k = std::fread(buf, 1, sizeof buf, f)) > 0) out.append(buf, k);
+    std::fclose(f);
     return out;
   }
 };

@@ -2,7 +2,7 @@
 # One GPU-box visit: tests, smoke, bench lines of every workload, CPU arm, and (with "ncu") the launch list plus one
 # full capture each of step_kernel (config 2) and policy_tc_kernel (16384 rows).
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q -x > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
+timeout 1500 python -m pytest tests -m gpu -q -x --durations=8 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench_config2.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench_config2.json; tail -3 gpurun_out/bench.err
 timeout 600 python bench.py --impl reference --steps 5 > gpurun_out/bench_ref_config2.json 2>&1; cat gpurun_out/bench_ref_config2.json
