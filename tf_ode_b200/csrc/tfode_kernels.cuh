@@ -276,11 +276,13 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   unsigned short* const myq = queue + (incl - qn);
 
   PG_MARK(0)
-  for (int it = 0; it < pgs_iters; it++) {
-    if ((it & 7) == 0) {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt, this island's slice of the env's stream
+  const int dummy_ent = (b << 8) | BR_SOLO;   // idle slot: row 0, one-body, partner = self, never fires
+  for (int it0 = 0; it0 < pgs_iters; it0 += 8) {
+    const int nsw = min(8, pgs_iters - it0);   // sweeps until the next reorder
+    {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt, this island's slice of the env's stream
       PG_MARK(3)
       if (leader && m > 1) {
-        uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it >> 3) * (m - 1)));
+        uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it0 >> 3) * (m - 1)));
         for (int q = 1; q < m; q++) {
           const int sw = lcg_randint(sd, (uint32_t)(q + 1));
           const unsigned char x = ord[q], y = ord[sw];
@@ -296,19 +298,91 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r, hdr, b);
       }
       __syncwarp();
-      PG_MARK(2)
     }
+    // Static firing schedule.  Which lock-step a row fires at depends only on the queues (a row fires when it heads the
+    // queues of both of its bodies), not on any value, so the integer part of the lock-step loop is run once per
+    // reorder: bit t of `mask0` = this lane relaxes its next queue entry at lock-step t; T = lock-steps per sweep.
+    unsigned long long mask0 = 0ull; int T = 0;
+    {
+      int cur = 0, ent = qn > 0 ? (int)myq[0] : dummy_ent;
+      while (__any_sync(FULLMASK, cur < qn)) {
+        const bool have = cur < qn;
+        const int myrow = have ? (ent & 127) : -1;
+        const int prow = __shfl_sync(FULLMASK, myrow, hbase | ((ent >> 8) & 15));
+        if (have && ((ent & BR_SOLO) || prow == myrow)) {
+          if (T < 64) mask0 |= 1ull << T;
+          cur++;
+          if (cur < qn) ent = myq[cur];
+        }
+        T++;
+      }
+    }
+    PG_MARK(2)
 #ifdef TFODE_PHASE_TIMING
-    if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[7], 1ull);
+    if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[7], (unsigned long long)nsw);
+    nsteps += nsw * T;
 #endif
-    // Lock-steps.  The kernel is instruction-issue bound here (two sweep warps per scheduler, in-order issue), so the
-    // loop is written for the fewest instructions per lock-step: queue entries are pre-decoded, the environment's
-    // shared-memory address is pinned in a register, and lambda of a row is read and written by ONE lane only (the
-    // lane of the row's first body, which is also the first body of the friction rows of the same contact) and reaches
-    // the partner inside the shuffle round -- no shared-memory ordering between lanes, no __syncwarp.
+    if (T >= 2 && T <= 64) {
+      // Lock-steps, software-pipelined over the static schedule: every lane takes every lock-step (idle slots carry a
+      // dummy entry and are predicated off), so the body is one basic block -- no readiness test, no vote, no divergent
+      // branch -- and the record of lock-step t+1 (queue entry, J, row constants, I^-1 J, lambda) is requested at the
+      // top of lock-step t, off the dependent chain fc -> J.fc -> shuffle -> delta -> fc.  lambda of a row is read and
+      // written by ONE lane only (the lane of the row's first body, which is also the first body of the friction rows
+      // of the same contact) and reaches the partner inside the shuffle round; the one read-after-write hazard the
+      // prefetch opens (a friction row right after its own normal row on the same lane) is closed by forwarding.
+      const int total = nsw * T;
+      int t = 0, cur = 0;
+      unsigned long long mrem = mask0;
+      BodyRow rb; float lam, lamf;
+      {
+        const int e0 = (mask0 & 1ull) ? (int)myq[0] : dummy_ent;
+        pgs_load_row(S, e0, iI, rb, lam);
+        lamf = S.rowS[(e0 & 127) - ((e0 >> 13) & 3)][RS_LAM];
+      }
+#pragma unroll 2
+      for (int i = 0; i < total; i++) {
+        const bool fire = (mrem & 1ull) != 0ull;
+        // ---- request lock-step t+1 (wraps into the next sweep)
+        int tn = t + 1, curn = cur + (fire ? 1 : 0);
+        unsigned long long mn = mrem >> 1;
+        if (tn == T) { tn = 0; curn = 0; mn = mask0; }
+        int en = dummy_ent;
+        if (mn & 1ull) en = myq[curn];
+        BodyRow rn; float lam_n, lamf_n;
+        pgs_load_row(S, en, iI, rn, lam_n);
+        const int nrow_n = (en & 127) - ((en >> 13) & 3);
+        lamf_n = S.rowS[nrow_n][RS_LAM];
+        // ---- relax the row of lock-step t
+        const int row = rb.meta & 127, pl = hbase | ((rb.meta >> 8) & 15);
+        const bool is1 = (rb.meta & BR_IS1) != 0, solo = (rb.meta & BR_SOLO) != 0, fric = (rb.meta >> 13) != 0;
+        const float part = tfn::dot6(rb.J, fc);
+        const float other = __shfl_sync(FULLMASK, part, pl);
+        const float lam_o = __shfl_sync(FULLMASK, lam, pl);
+        const float lamf_o = __shfl_sync(FULLMASK, lamf, pl);
+        const float lam_c = is1 ? lam : lam_o, lamf_c = is1 ? lamf : lamf_o;
+        float lo = rb.lo, hi = rb.hi;
+        if (fric) { hi = fabsf(hi * lamf_c); lo = -hi; }
+        const float sum = solo ? part : (is1 ? part + other : other + part);
+        float delta = tfn::fma(rb.Ad, rb.rhs - sum, -(lam_c * rb.Adcfm));
+        float nl = lam_c + delta;
+        if (nl < lo) { delta = lo - lam_c; nl = lo; }
+        else if (nl > hi) { delta = hi - lam_c; nl = hi; }
+        if (fire && is1) S.rowS[row][RS_LAM] = nl;
+        const float dm = delta * invM;
+        const float f0 = tfn::fma(dm, rb.J[0], fc[0]), f1 = tfn::fma(dm, rb.J[1], fc[1]), f2 = tfn::fma(dm, rb.J[2], fc[2]);
+        const float f3 = tfn::fma(delta, rb.a[0], fc[3]), f4 = tfn::fma(delta, rb.a[1], fc[4]), f5 = tfn::fma(delta, rb.a[2], fc[5]);
+        fc[0] = fire ? f0 : fc[0]; fc[1] = fire ? f1 : fc[1]; fc[2] = fire ? f2 : fc[2];
+        fc[3] = fire ? f3 : fc[3]; fc[4] = fire ? f4 : fc[4]; fc[5] = fire ? f5 : fc[5];
+        if (fire && nrow_n == row) lamf_n = nl;   // the normal row of the next (friction) row was relaxed just now
+        rb = rn; lam = lam_n; lamf = lamf_n; t = tn; cur = curn; mrem = mn;
+      }
+    } else {
+    // Fallback (a body with more than 64 rows, or single-row chains): the same lock-steps with the readiness test done on
+    // the fly -- queue entries pre-decoded, lambda owned by one lane and exchanged in the shuffle round, no __syncwarp.
+    for (int sw_i = 0; sw_i < nsw; sw_i++) {
     int cur = 0;
     BodyRow rb;
-    rb.meta = (b << 8) | BR_SOLO; rb.rhs = 0; rb.Ad = 0; rb.Adcfm = 0; rb.lo = 0; rb.hi = 0;
+    rb.meta = dummy_ent; rb.rhs = 0; rb.Ad = 0; rb.Adcfm = 0; rb.lo = 0; rb.hi = 0;
 #pragma unroll
     for (int k = 0; k < 6; k++) rb.J[k] = 0;
     rb.a[0] = 0; rb.a[1] = 0; rb.a[2] = 0;
@@ -317,9 +391,6 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     float lamf = S.rowS[(rb.meta & 127) - ((rb.meta >> 13) & 3)][RS_LAM];
     int ent_next = (qn > 1) ? myq[1] : rb.meta;
     while (__any_sync(FULLMASK, cur < qn)) {
-#ifdef TFODE_PHASE_TIMING
-      nsteps++;
-#endif
       const bool have = cur < qn;
       const int row = rb.meta & 127, pl = hbase | ((rb.meta >> 8) & 15);
       const bool is1 = (rb.meta & BR_IS1) != 0, solo = (rb.meta & BR_SOLO) != 0, fric = (rb.meta >> 13) != 0;
@@ -350,6 +421,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
           if (cur + 1 < qn) ent_next = myq[cur + 1];
         }
       }
+    }
+    }
     }
     __syncwarp();
   }
