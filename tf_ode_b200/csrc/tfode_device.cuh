@@ -108,6 +108,9 @@ struct StepParams {
   float* trans; int trans_cap; int* n_trans;
   // external commands
   const float* ext_speed;  // NULL or [n_envs]
+  // tire-sphere centres in the wheel frame (Model::ring, padded to float4) in global memory: the lanes of a warp read 32
+  // different entries at once, which the constant cache would serialise
+  const float4* ring4;
 };
 
 }  // namespace tfode

@@ -177,9 +177,13 @@ __device__ unsigned long long g_phase_cycles[16];
 #define PT_DECL long long pt_t = clock64(); long long pt_acc[6] = {0, 0, 0, 0, 0, 0};
 #define PT_MARK(i) { long long t_ = clock64(); pt_acc[i] += t_ - pt_t; pt_t = t_; }
 #define PT_FLUSH if (threadIdx.x == 0) { for (int i_ = 0; i_ < 6; i_++) atomicAdd(&g_phase_cycles[i_], (unsigned long long)pt_acc[i_]); }
+#define PC_DECL long long pc_t = clock64();
+#define PC_MARK(i) { long long t_ = clock64(); if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[12 + i], (unsigned long long)(t_ - pc_t)); pc_t = t_; }
 #define PG_DECL long long pg_t = clock64();
 #define PG_MARK(i) { long long t_ = clock64(); if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[8 + i], (unsigned long long)(t_ - pg_t)); pg_t = t_; }
 #else
+#define PC_DECL
+#define PC_MARK(i)
 #define PG_DECL
 #define PG_MARK(i)
 #define PT_DECL
@@ -283,16 +287,27 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       PG_MARK(3)
       if (leader && m > 1) {
         uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it0 >> 3) * (m - 1)));
-        for (int q = 1; q < m; q++) {
-          const int sw = lcg_randint(sd, (uint32_t)(q + 1));
+        int sw = lcg_randint(sd, 2u);
+        for (int q = 1; q < m; q++) {   // the draw of the next swap (LCG step, bit folds, modulo) overlaps the shared-memory round trip of this one
+          const int sw_next = lcg_randint(sd, (uint32_t)(q + 2));
           const unsigned char x = ord[q], y = ord[sw];
           ord[q] = y; ord[sw] = x;
+          sw = sw_next;
         }
       }
       __syncwarp();
       PG_MARK(1)
-      int i = 0;
-      for (int k = 0; k < m; k++) {
+      int i = 0, k = 0;
+      for (; k + 4 <= m; k += 4) {   // four rows per round: the two dependent loads (order -> row header) of the four overlap
+        const int r0 = ord[k], r1 = ord[k + 1], r2 = ord[k + 2], r3 = ord[k + 3];
+        const int h0 = __float_as_int(S.rowS[r0][RS_HDR]), h1 = __float_as_int(S.rowS[r1][RS_HDR]);
+        const int h2 = __float_as_int(S.rowS[r2][RS_HDR]), h3 = __float_as_int(S.rowS[r3][RS_HDR]);
+        if ((h0 & 15) == b || ((h0 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r0, h0, b);
+        if ((h1 & 15) == b || ((h1 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r1, h1, b);
+        if ((h2 & 15) == b || ((h2 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r2, h2, b);
+        if ((h3 & 15) == b || ((h3 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r3, h3, b);
+      }
+      for (; k < m; k++) {
         const int r = ord[k];
         const int hdr = __float_as_int(S.rowS[r][RS_HDR]);
         if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r, hdr, b);
@@ -524,6 +539,8 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
       // ------------------------------------------------------------ collide (ode/environment.cc:56-150)
       int nc_total = 0;    // generated contacts (uniform)
       unsigned fork_hit = 0;
+      unsigned hfpre[7] = {0, 0, 0, 0, 0, 0, 0};   // heightfield scene: spheres low enough to reach the map (one bit per sphere, sphere order)
+      PC_DECL
       const int n_terrain = (cfg.scene == TFODE_SCENE_STEP_BOXES) ? 3 : (cfg.scene == TFODE_SCENE_HEIGHTFIELD ? 2 : 1);
       for (int t = 0; t < n_terrain; t++) {
         const int tkind = (t == 0) ? T_PLANE : (cfg.scene == TFODE_SCENE_STEP_BOXES ? T_BOX : T_HF);
@@ -533,6 +550,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
         const float* tside = M.step_side[(tkind == T_BOX) ? (t - 1) : 0];
         for (int pass = 0; pass < 8; pass++) {
           CG cg[4]; int n = 0; int gbody = 0; int soft = 0;
+          PC_MARK(3)
           if (pass == 0) {
             if (lane < NNS) {
               const int g = lane;
@@ -584,22 +602,36 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
                 else n = col_box_samples(tkind, gp, gR, dim, tpos, tR, tside, P.hf, cg);
               }
             }
-          } else {
-            const int s = (pass - 1) * 32 + lane;
-            float c[3] = {0, 0, 0}, cl[3] = {0, 0, 0}; int rng[4] = {0, 0, 0, 0};
-            bool cand = false;
-            if (s < NSPHERE) {
-              const int w = s / 50, k = s - w * 50;
-              gbody = 6 + w; soft = (k == 49);
-              const float* bR = S.bR[gbody];
-              mulRv(c, bR, M.ring[k]);  // dBodyGetRelPointPos of the geom offset (ode/wheel.hh:70-72)
-              c[0] += S.bpos[gbody][0]; c[1] += S.bpos[gbody][1]; c[2] += S.bpos[gbody][2];
-              if (tkind == T_PLANE) n = col_sphere_plane(c, M.sphere_r, cg);
-              else if (tkind == T_BOX) n = col_sphere_box(c, M.sphere_r, tpos, tR, tside, cg);
-              else cand = hf_sphere_range(P.hf, c, M.sphere_r, cl, rng);
-            }
-            if (tkind == T_HF) {  // the warp scans the candidate spheres one at a time, in sphere order
+            if (tkind != T_PLANE) { PC_MARK(0) }
+          } else if (tkind == T_HF) {
+            // Candidate spheres were picked while the plane was tested (hfpre[]: bit = the sphere's lowest point is not
+            // above the highest vertex of the map).  They are compacted in sphere order, 32 per round: a lane takes one
+            // candidate through the block-maxima range test, then the whole warp scans the survivors one at a time.
+            if (pass > 1) continue;
+            int ncand = 0;
+#pragma unroll
+            for (int j = 0; j < 7; j++) ncand += __popc(hfpre[j]);
+            for (int base_c = 0; base_c < ncand; base_c += 32) {
+              int want = base_c + lane, s = -1;
+#pragma unroll
+              for (int j = 0; j < 7; j++) {
+                const int pc = __popc(hfpre[j]);
+                if (s < 0 && want >= 0 && want < pc) s = j * 32 + (int)__fns(hfpre[j], 0, want + 1);
+                want -= pc;
+              }
+              float c[3] = {0, 0, 0}, cl[3] = {0, 0, 0}; int rng[4] = {0, 0, 0, 0};
+              bool cand = false;
+              if (s >= 0) {
+                const int w = s / 50, k = s - w * 50;
+                gbody = 6 + w; soft = (k == 49);
+                const float4 rk = __ldg(P.ring4 + k);
+                const float ring_k[3] = {rk.x, rk.y, rk.z};
+                mulRv(c, S.bR[gbody], ring_k);
+                c[0] += S.bpos[gbody][0]; c[1] += S.bpos[gbody][1]; c[2] += S.bpos[gbody][2];
+                cand = hf_sphere_range(P.hf, c, M.sphere_r, cl, rng);
+              }
               unsigned cm = __ballot_sync(FULLMASK, cand);
+              PC_MARK(1)
               while (cm) {
                 const int src = __ffs(cm) - 1; cm &= cm - 1;
                 float cw_[3], cl_[3]; int rg_[4];
@@ -610,8 +642,25 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
                 const int info = __shfl_sync(FULLMASK, gbody | (tbody << 4) | (soft << 8), src);
                 nc_total += col_sphere_hf_warp(P.hf, cw_, cl_, M.sphere_r, rg_, lane, S.cont, nc_total, maxc, info);
               }
-              continue;
+              PC_MARK(2)
             }
+            continue;
+          } else {
+            const int s = (pass - 1) * 32 + lane;
+            float c[3] = {0, 0, 0};
+            bool pre = false;
+            if (s < NSPHERE) {
+              const int w = s / 50, k = s - w * 50;
+              gbody = 6 + w; soft = (k == 49);
+              const float4 rk = __ldg(P.ring4 + k);
+              const float ring_k[3] = {rk.x, rk.y, rk.z};
+              mulRv(c, S.bR[gbody], ring_k);  // dBodyGetRelPointPos of the geom offset (ode/wheel.hh:70-72)
+              c[0] += S.bpos[gbody][0]; c[1] += S.bpos[gbody][1]; c[2] += S.bpos[gbody][2];
+              if (tkind == T_PLANE) n = col_sphere_plane(c, M.sphere_r, cg);
+              else n = col_sphere_box(c, M.sphere_r, tpos, tR, tside, cg);
+              if (cfg.scene == TFODE_SCENE_HEIGHTFIELD) pre = !((c[2] - P.hf.pos[2]) - M.sphere_r > P.hf.hmax);   // hf_to_local's height, hf_sphere_range's last test with zm <= hmax
+            }
+            if (tkind == T_PLANE && cfg.scene == TFODE_SCENE_HEIGHTFIELD) hfpre[pass - 1] = __ballot_sync(FULLMASK, pre);
           }
           if (__any_sync(FULLMASK, n > 0)) {
             int incl = warp_incl_scan(n, lane);

@@ -37,5 +37,7 @@ for nm, v in zip(names, out[:6]):
 print("pgs: %.1f lock-steps per sweep (warp 0 of each CTA), %d sweeps" % (out[6] / max(out[7], 1), out[7]))
 for nm, v in zip(["pgs: queue sizes", "pgs: Fisher-Yates", "pgs: queue fill", "pgs: sweeps"], out[8:12]):
     print("  %-24s %8.0f cycles per CTA-substep" % (nm, v / ncta / 300))
+for nm, v in zip(["collide: non-sphere geoms vs box/hf", "collide: sphere range tests (hf)", "collide: sphere-hf warp scans", "collide: rest (plane, compaction)"], out[12:16]):
+    print("  %-36s %8.0f cycles per CTA-substep" % (nm, v / ncta / 300))
 print("  per lock-step: %.0f cycles" % (out[11] / max(out[6], 1) * 1.0))
 print("total %.0f cycles per CTA-substep (%s, %d envs)" % (tot / ncta / 300, wl, n))
