@@ -289,7 +289,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it0 >> 3) * (m - 1)));
         int sw = lcg_randint(sd, 2u);
         for (int q = 1; q < m; q++) {   // the draw of the next swap (LCG step, bit folds, modulo) overlaps the shared-memory round trip of this one
-          const int sw_next = lcg_randint(sd, (uint32_t)(q + 2));
+          const int sw_next = lcg_randint_magic(sd, (uint32_t)(q + 2), c_fy_magic.v[q + 2]);
           const unsigned char x = ord[q], y = ord[sw];
           ord[q] = y; ord[sw] = x;
           sw = sw_next;
@@ -337,7 +337,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     if (threadIdx.x == 0) atomicAdd(&g_phase_cycles[7], (unsigned long long)nsw);
     nsteps += nsw * T;
 #endif
-    if (T >= 2 && T <= 64) {
+    if (T >= 2 && T <= 32) {
       // Lock-steps, software-pipelined over the static schedule: every lane takes every lock-step (idle slots carry a
       // dummy entry and are predicated off), so the body is one basic block -- no readiness test, no vote, no divergent
       // branch -- and the record of lock-step t+1 (queue entry, J, row constants, I^-1 J, lambda) is requested at the
@@ -345,29 +345,19 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       // written by ONE lane only (the lane of the row's first body, which is also the first body of the friction rows
       // of the same contact) and reaches the partner inside the shuffle round; the one read-after-write hazard the
       // prefetch opens (a friction row right after its own normal row on the same lane) is closed by forwarding.
-      const int total = nsw * T;
-      int t = 0, cur = 0;
-      unsigned long long mrem = mask0;
+      const unsigned mask32 = (unsigned)mask0;
       BodyRow rb; float lam, lamf;
       {
-        const int e0 = (mask0 & 1ull) ? (int)myq[0] : dummy_ent;
+        const int e0 = (mask32 & 1u) ? (int)myq[0] : dummy_ent;
         pgs_load_row(S, e0, iI, rb, lam);
         lamf = S.rowS[(e0 & 127) - ((e0 >> 13) & 3)][RS_LAM];
       }
-#pragma unroll 2
-      for (int i = 0; i < total; i++) {
-        const bool fire = (mrem & 1ull) != 0ull;
-        // ---- request lock-step t+1 (wraps into the next sweep)
-        int tn = t + 1, curn = cur + (fire ? 1 : 0);
-        unsigned long long mn = mrem >> 1;
-        if (tn == T) { tn = 0; curn = 0; mn = mask0; }
-        int en = dummy_ent;
-        if (mn & 1ull) en = myq[curn];
+      // one lock-step: `fire` = this lane relaxes rb now; `en` = its queue entry for the next lock-step
+      auto lock_step = [&](const bool fire, const int en) {
         BodyRow rn; float lam_n, lamf_n;
         pgs_load_row(S, en, iI, rn, lam_n);
         const int nrow_n = (en & 127) - ((en >> 13) & 3);
         lamf_n = S.rowS[nrow_n][RS_LAM];
-        // ---- relax the row of lock-step t
         const int row = rb.meta & 127, pl = hbase | ((rb.meta >> 8) & 15);
         const bool is1 = (rb.meta & BR_IS1) != 0, solo = (rb.meta & BR_SOLO) != 0, fric = (rb.meta >> 13) != 0;
         const float part = tfn::dot6(rb.J, fc);
@@ -389,10 +379,26 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         fc[0] = fire ? f0 : fc[0]; fc[1] = fire ? f1 : fc[1]; fc[2] = fire ? f2 : fc[2];
         fc[3] = fire ? f3 : fc[3]; fc[4] = fire ? f4 : fc[4]; fc[5] = fire ? f5 : fc[5];
         if (fire && nrow_n == row) lamf_n = nl;   // the normal row of the next (friction) row was relaxed just now
-        rb = rn; lam = lam_n; lamf = lamf_n; t = tn; cur = curn; mrem = mn;
+        rb = rn; lam = lam_n; lamf = lamf_n;
+      };
+      const unsigned short* qp0 = myq;
+      const int e_first = (mask32 & 1u) ? (int)myq[0] : dummy_ent;
+      for (int sw_i = 0; sw_i < nsw; sw_i++) {
+        unsigned mrem = mask32;
+        const unsigned short* qp = qp0;
+#pragma unroll 2
+        for (int t = 0; t < T - 1; t++) {
+          const bool fire = (mrem & 1u) != 0u;
+          qp += fire ? 1 : 0;
+          mrem >>= 1;
+          int en = dummy_ent;
+          if (mrem & 1u) en = *qp;
+          lock_step(fire, en);
+        }
+        lock_step((mrem & 1u) != 0u, e_first);   // last lock-step of the sweep: the next one is lock-step 0 again
       }
     } else {
-    // Fallback (a body with more than 64 rows, or single-row chains): the same lock-steps with the readiness test done on
+    // Fallback (more than 32 lock-steps per sweep, or single-row chains): the same lock-steps with the readiness test done on
     // the fly -- queue entries pre-decoded, lambda owned by one lane and exchanged in the shuffle round, no __syncwarp.
     for (int sw_i = 0; sw_i < nsw; sw_i++) {
     int cur = 0;

@@ -130,6 +130,26 @@ __device__ __forceinline__ uint32_t lcg_jump(uint32_t seed, uint32_t k) {
   }
   return accA * seed + accC;
 }
+struct FyMagic { uint32_t v[MAXROWS + 4]; };
+constexpr FyMagic make_fy_magic() { FyMagic t{}; for (int i = 1; i < MAXROWS + 4; i++) t.v[i] = 0xffffffffu / (uint32_t)i; return t; }
+__constant__ FyMagic c_fy_magic = make_fy_magic();   // floor((2^32 - 1) / un), read with a warp-uniform index
+
+// dRandInt with the modulo done by a reciprocal multiply: magic = floor((2^32 - 1) / un) makes umulhi(r, magic) fall short of
+// floor(r / un) by at most 2, which two conditional subtractions repair -- exact for every r, and the generic 32-bit
+// division (the longest dependent stretch of the Fisher-Yates draw) leaves the chain; magic depends on un only.
+__device__ __forceinline__ int lcg_randint_magic(uint32_t& seed, uint32_t un, uint32_t magic) {
+  seed = 1664525u * seed + 1013904223u;
+  uint32_t r = seed;
+  if (un <= 0x00010000u) { r ^= (r >> 16);
+    if (un <= 0x00000100u) { r ^= (r >> 8);
+      if (un <= 0x00000010u) { r ^= (r >> 4);
+        if (un <= 0x00000004u) { r ^= (r >> 2);
+          if (un <= 0x00000002u) r ^= (r >> 1); } } } }
+  uint32_t rem = r - __umulhi(r, magic) * un;
+  if (rem >= un) rem -= un;
+  if (rem >= un) rem -= un;
+  return (int)rem;
+}
 __device__ __forceinline__ int lcg_randint(uint32_t& seed, uint32_t un) {  // dRandInt
   seed = 1664525u * seed + 1013904223u;
   uint32_t r = seed;
