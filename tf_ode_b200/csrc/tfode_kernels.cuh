@@ -218,6 +218,13 @@ __device__ __forceinline__ int pgs_make_entry(int row, int hdr, int b) {
   const int pb = solo ? b : (is1 ? b2 : b1), fo = fidx != 255 ? row - fidx : 0;
   return row | (is1 ? BR_IS1 : 0) | (pb << 8) | (solo ? BR_SOLO : 0) | (fo << 13);
 }
+// appends the entry of a row (packed pair pk, see RS_ENT) to the queue of body b if the row touches b
+__device__ __forceinline__ void pgs_push(unsigned short*& qw, int pk, int b) {
+  const bool is1 = ((pk >> 24) & 15) == b, is2 = ((pk >> 8) & 15) == b;
+  const int ent = is1 ? (pk & 0xffff) : ((pk >> 16) & 0xffff);
+  if (is1 || is2) *qw = (unsigned short)ent;
+  qw += (is1 || is2) ? 1 : 0;
+}
 // static part of a row for this lane's body; lam = the row's lambda as stored right now
 __device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const float* iI, BodyRow& r, float& lam) {
   const int row = entry & 127;
@@ -271,8 +278,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   // rows per body (does not depend on the permutation) -> start of each body's queue
   int qn = 0;
   for (int k = 0; k < m; k++) {
-    const int hdr = __float_as_int(S.rowS[ord[k]][RS_HDR]);
-    if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) qn++;
+    const int pk = __float_as_int(S.rowS[ord[k]][RS_ENT]);
+    if (((pk >> 24) & 15) == b || ((pk >> 8) & 15) == b) qn++;
   }
   int incl = qn;
 #pragma unroll
@@ -297,21 +304,18 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       }
       __syncwarp();
       PG_MARK(1)
-      int i = 0, k = 0;
-      for (; k + 4 <= m; k += 4) {   // four rows per round: the two dependent loads (order -> row header) of the four overlap
+      // Queue fill.  Every row carries its two pre-decoded entries (RS_ENT); an entry's partner field names the OTHER body, so
+      // this lane's body is body 1 of the row iff the second entry's partner is b, body 2 iff the first entry's partner is b
+      // (a one-body row names its own body in both, and its lane takes the first).  Branch-free, four rows per round.
+      unsigned short* qw = myq;
+      int k = 0;
+      for (; k + 4 <= m; k += 4) {
         const int r0 = ord[k], r1 = ord[k + 1], r2 = ord[k + 2], r3 = ord[k + 3];
-        const int h0 = __float_as_int(S.rowS[r0][RS_HDR]), h1 = __float_as_int(S.rowS[r1][RS_HDR]);
-        const int h2 = __float_as_int(S.rowS[r2][RS_HDR]), h3 = __float_as_int(S.rowS[r3][RS_HDR]);
-        if ((h0 & 15) == b || ((h0 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r0, h0, b);
-        if ((h1 & 15) == b || ((h1 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r1, h1, b);
-        if ((h2 & 15) == b || ((h2 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r2, h2, b);
-        if ((h3 & 15) == b || ((h3 >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r3, h3, b);
+        const int p0 = __float_as_int(S.rowS[r0][RS_ENT]), p1 = __float_as_int(S.rowS[r1][RS_ENT]);
+        const int p2 = __float_as_int(S.rowS[r2][RS_ENT]), p3 = __float_as_int(S.rowS[r3][RS_ENT]);
+        pgs_push(qw, p0, b); pgs_push(qw, p1, b); pgs_push(qw, p2, b); pgs_push(qw, p3, b);
       }
-      for (; k < m; k++) {
-        const int r = ord[k];
-        const int hdr = __float_as_int(S.rowS[r][RS_HDR]);
-        if ((hdr & 15) == b || ((hdr >> 4) & 15) == b) myq[i++] = (unsigned short)pgs_make_entry(r, hdr, b);
-      }
+      for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k]][RS_ENT]), b);
       __syncwarp();
     }
     // Static firing schedule.  Which lock-step a row fires at depends only on the queues (a row fires when it heads the
@@ -893,6 +897,8 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
         Sr[RS_RHS] = tfn::fma(Sr[RS_C], fps, -s);
         Sr[RS_AD] = Ad;
         Sr[RS_ADCFM] = Ad * cfm_h;
+        // c is consumed: its slot now holds the row's two pre-decoded sweep-queue entries (body 1's lane | body 2's lane << 16)
+        Sr[RS_ENT] = __int_as_float(pgs_make_entry(r, hdr, b1) | ((b2 < NB ? pgs_make_entry(r, hdr, b2) : (b1 << 8)) << 16));
       }
 
       // ------------------------------------------------------------ constraint order per island (quickstep.cpp SOR_LCP)

@@ -47,7 +47,7 @@ struct __align__(16) WarpSm {
 };
 static_assert(sizeof(EnvRec) <= sizeof(float) * MAXROWS * 12, "record staging aliases the row array");
 
-enum { RS_RHS = 0, RS_AD = 1, RS_ADCFM = 2, RS_LO = 3, RS_HI = 4, RS_LAM = 5, RS_HDR = 6, RS_C = 7 };
+enum { RS_RHS = 0, RS_AD = 1, RS_ADCFM = 2, RS_LO = 3, RS_HI = 4, RS_LAM = 5, RS_HDR = 6, RS_C = 7, RS_ENT = 7 };
 
 // ---------------------------------------------------------------- small math
 // fma placement of these products is fixed by the numerics contract (include/tfode_numerics.h); the kernels are
