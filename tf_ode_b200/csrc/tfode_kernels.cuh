@@ -580,8 +580,19 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
                 for (int k = 0; k < 9; k++) gR[k] = bR[k];
               }
               const float* dim = M.ns_dim[g];
-              if (M.ns_type[g] == 2) {
-                if (tkind == T_PLANE) n = col_cyl_plane(gp, gR, dim[0], dim[1], cg);
+              // Conservative reject: the lowest point the geom can reach, against the highest point of the terrain piece
+              // (0 for the plane, the top of the map, the top of the step box).  The margin is three orders of magnitude
+              // above the rounding of these sums, so a skipped collider is one that would have returned no contact.
+              const bool is_cyl = M.ns_type[g] == 2;
+              const float reach = is_cyl ? (0.5f * dim[1] * fabsf(gR[8]) + dim[0])
+                                         : 0.5f * (fabsf(gR[6]) * dim[0] + fabsf(gR[7]) * dim[1] + fabsf(gR[8]) * dim[2]);
+              const float top = (tkind == T_PLANE) ? 0.0f
+                              : (tkind == T_HF) ? (P.hf.pos[2] + P.hf.hmax)
+                                                : (tpos[2] + 0.5f * (fabsf(tR[6]) * tside[0] + fabsf(tR[7]) * tside[1] + fabsf(tR[8]) * tside[2]));
+              const bool may_touch = !(gp[2] - reach > top + 1e-4f);
+              if (is_cyl) {
+                if (!may_touch) n = 0;
+                else if (tkind == T_PLANE) n = col_cyl_plane(gp, gR, dim[0], dim[1], cg);
                 else n = col_cyl_samples(tkind, gp, gR, dim[0], dim[1], tpos, tR, tside, P.hf, cg);
                 if (M.ns_cb[g] && cfg.fork_callback) {  // near-callback AABB test (Q10)
                   float lo[3], hi[3];
@@ -608,7 +619,8 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
                   if (ov) fork_hit = 1;
                 }
               } else {
-                if (tkind == T_PLANE) n = col_box_plane(gp, gR, dim, cg);
+                if (!may_touch) n = 0;
+                else if (tkind == T_PLANE) n = col_box_plane(gp, gR, dim, cg);
                 else n = col_box_samples(tkind, gp, gR, dim, tpos, tR, tside, P.hf, cg);
               }
             }
