@@ -29,7 +29,7 @@ struct TfodeBatch {
   float* policy_in = nullptr; int* parked_list = nullptr; int* n_parked = nullptr;
   float* trans = nullptr; int* n_trans = nullptr; int trans_cap = 0;
   float* ext_speed = nullptr;
-  float4* ring4 = nullptr;    // Model::ring as float4 in global memory
+  float4* ring4 = nullptr; Model* model_g = nullptr;    // Model::ring as float4 in global memory
   float* weights = nullptr;   // fp32 W1 b1 W2 b2 W3 b3
   PolicyTC tc;                // bf16 operand copies for the tcgen05 path
   bool has_policy = false;
@@ -281,6 +281,8 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   {
     float4 r4[50];
     for (int k = 0; k < 50; k++) r4[k] = make_float4(M.ring[k][0], M.ring[k][1], M.ring[k][2], 0.0f);
+    CKC(cudaMalloc(&b->model_g, sizeof(Model)));
+    CKC(cudaMemcpy(b->model_g, &M, sizeof(Model), cudaMemcpyHostToDevice));
     CKC(cudaMalloc(&b->ring4, sizeof(r4)));
     CKC(cudaMemcpy(b->ring4, r4, sizeof(r4), cudaMemcpyHostToDevice));
   }
@@ -305,7 +307,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   std::memset(&P, 0, sizeof(P));
   P.rec = b->rec; P.budget = b->budget; P.n_envs = n; P.set_budget = -1; P.cfg = *cfg; P.cfg.hf_heights = nullptr;
   P.policy_in = b->policy_in; P.parked_list = b->parked_list; P.n_parked = b->n_parked;
-  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.ext_speed = nullptr; P.ring4 = b->ring4;
+  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.ext_speed = nullptr; P.ring4 = b->ring4; P.model = b->model_g;
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD) {
     const int nc = cfg->hf_ncol, nr = cfg->hf_nrow;
     const int nbx = (nc + 7) / 8, nbz = (nr + 7) / 8;
@@ -344,7 +346,7 @@ void tfode_batch_destroy(TfodeBatch* b) {
   if (!b) return;
   for (int t = 0; t < 2; t++) { cudaFree(b->tree_nodes[t]); cudaFree(b->tree_params[t]); }
   cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
-  cudaFree(b->n_parked); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
+  cudaFree(b->n_parked); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
   cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
   policy_tc_free(b->tc);
   if (b->h_pin) cudaFreeHost(b->h_pin);

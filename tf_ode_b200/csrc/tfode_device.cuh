@@ -111,6 +111,9 @@ struct StepParams {
   // tire-sphere centres in the wheel frame (Model::ring, padded to float4) in global memory: the lanes of a warp read 32
   // different entries at once, which the constant cache would serialise
   const float4* ring4;
+  // the model tables once more in global memory: per-lane indexed reads (body / joint / geom tables) gather through L1
+  // instead of being serialised address by address by the constant cache
+  const Model* model;
 };
 
 }  // namespace tfode

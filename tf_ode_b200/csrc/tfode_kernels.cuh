@@ -462,6 +462,9 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   }
 }
 
+#ifndef TFODE_MODEL_SRC
+#define TFODE_MODEL_SRC (*P.model)
+#endif
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -469,7 +472,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepPa
   const bool valid = env < P.n_envs;
   WarpSm* const sm = reinterpret_cast<WarpSm*>(smem_raw);
   WarpSm& S = sm[wid];
-  const Model& M = g_model;
+  const Model& M = TFODE_MODEL_SRC;   // A/B switch: constant memory (g_model) or the global-memory copy (*P.model)
   const TfodeBatchConfig& cfg = P.cfg;
   const uint32_t env_global = (uint32_t)(cfg.env_id_offset + env);
 
