@@ -5,7 +5,10 @@
 namespace tfode {
 
 constexpr int WARPS_PER_CTA = 4;   // reset kernel
-constexpr int ENVS_PER_CTA = 8;    // step kernel: 8 environments = 8 warps per CTA, 2 CTAs per SM
+#ifndef TFODE_ENVS_PER_CTA
+#define TFODE_ENVS_PER_CTA 8
+#endif
+constexpr int ENVS_PER_CTA = TFODE_ENVS_PER_CTA;    // step kernel: one warp per environment; 16 environments resident per SM (registers and shared memory alike)
 
 // warp-inclusive scan of small counts
 __device__ __forceinline__ int warp_incl_scan(int v, int lane) {
@@ -465,7 +468,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
 #ifndef TFODE_MODEL_SRC
 #define TFODE_MODEL_SRC (*P.model)
 #endif
-__global__ void __launch_bounds__(ENVS_PER_CTA * 32, 2) step_kernel(const StepParams P) {
+__global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int env = blockIdx.x * ENVS_PER_CTA + wid;
