@@ -13,11 +13,15 @@ torch = pytest.importorskip("torch")
 FAST = dict(speedf=0.5, x_goal=0.6)   # episodes of a few seconds instead of a minute
 
 
-def _oracle_rows(n, exploration, steps):
+def _oracle_rows(n, exploration):
+    """Every episode to its end (goal, y_max, upside-down or the 60 s timeout), like training_module._run_episodes."""
     cfg = make_config(abi.PRESET_TRAINING, n, auto_reset=0, exploration=int(exploration), transition_capacity=n * 122, **FAST)
     o = oracle_lib.Oracle(cfg, "float", threads=8)
     o.load_policy(glorot_policy())
-    o.step(steps)
+    for _ in range(61):
+        o.step(1000)
+        if all(o.get_state(e).episodes_done == 1 for e in range(n)):
+            break
     rows = o.drain_transitions()
     states = [o.get_state(e) for e in range(n)]
     o.close()
@@ -27,8 +31,8 @@ def _oracle_rows(n, exploration, steps):
 def test_trial_returns_the_reference_tuples_and_matches_the_oracle():
     n = 12
     exp = training_module.trial(glorot_policy(), n_episodes=n, **FAST)
-    rows_o, states = _oracle_rows(n, True, 12000)
-    assert all(s.episodes_done == 1 for s in states), "oracle episodes did not all finish: lengthen the horizon"
+    rows_o, states = _oracle_rows(n, True)
+    assert all(s.episodes_done == 1 for s in states)
     want = training_module.rows_to_experience(rows_o, n)
     assert len(exp) == n
     for e in range(n):
@@ -46,7 +50,7 @@ def test_eval_prints_the_reference_result_line():
     n = 4
     buf = io.StringIO()
     res = training_module.eval(glorot_policy(), n_episodes=n, colour=False, file=buf, **FAST)
-    _, states = _oracle_rows(n, False, 12000)
+    _, states = _oracle_rows(n, False)
     lines = buf.getvalue().strip().splitlines()
     assert len(lines) == n
     for e, (line, s) in enumerate(zip(lines, states)):
