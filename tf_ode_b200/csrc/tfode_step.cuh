@@ -439,44 +439,28 @@ __device__ int col_sphere_hf_warp(const HfParams& hf, const float* cw, const flo
       live = !(dx * dx + dy * dy + dz * dz >= r2);
     }
     const unsigned lm = __ballot_sync(FULLMASK, live);
-    if (lm == 0u) continue;
-    // Feature tests, feature-major: lane k takes the k-th surviving cell and the six features are tried one after the other,
-    // so a pass runs ONE code path (vertex / edge / face) for the whole warp instead of six divergent ones.  The canonical
-    // order (cells ascending; per cell vertex, x-edge, z-edge, diagonal, face0, face1) is restored from the six hit masks.
-    const int nlive = __popc(lm);
-    int cix = 0, ciz = 0;
-    if (lane < nlive) { const int cl = base + (int)__fns(lm, 0, lane + 1); cix = ix0 + cl % ncx; ciz = iz0 + cl / ncx; }
-    unsigned hm[6]; unsigned any = 0u;
-#pragma unroll
-    for (int f = 0; f < 6; f++) {
-      bool hit = false; float nl[3], dist;
-      if (lane < nlive) hit = hf_feature(hf, c, r, cix, ciz, f, nl, &dist);
-      hm[f] = __ballot_sync(FULLMASK, hit);
-      any |= hm[f];
-    }
-    if (any == 0u) continue;
-    int before = 0, mine = 0;   // hits of lower cells; hits of my cell so far
-#pragma unroll
-    for (int f = 0; f < 6; f++) before += __popc(hm[f] & lt);
-#pragma unroll
-    for (int f = 0; f < 6; f++) {
-      if (hm[f] == 0u) continue;   // warp-uniform
-      if ((hm[f] >> lane) & 1u) {
-        float nl[3] = {0, 0, 0}, dist = 0;
-        hf_feature(hf, c, r, cix, ciz, f, nl, &dist);   // same inputs, same result as in the mask pass
-        const int slot = cnt + before + mine;
+    const int nitems = __popc(lm) * 6;
+    for (int i0 = 0; i0 < nitems; i0 += 32) {
+      const int item = i0 + lane;
+      bool hit = false; float nl[3] = {0, 0, 0}, dist = 0;
+      if (item < nitems) {
+        const int k = item / 6, f = item - k * 6;
+        const int cl = base + (int)__fns(lm, 0, k + 1);
+        hit = hf_feature(hf, c, r, ix0 + cl % ncx, iz0 + cl / ncx, f, nl, &dist);
+      }
+      const unsigned hm = __ballot_sync(FULLMASK, hit);
+      if (hit) {
+        const int slot = cnt + __popc(hm & lt);
         if (slot < 4 && slot0 + slot < maxc) {
           float* d = cont[slot0 + slot];
           const float nw0 = nl[0], nw1 = -nl[2], nw2 = nl[1];
           d[0] = cw[0] - nw0 * r; d[1] = cw[1] - nw1 * r; d[2] = cw[2] - nw2 * r; d[3] = nw0; d[4] = nw1; d[5] = nw2;
           d[6] = r - dist; d[7] = __int_as_float(info);
         }
-        mine++;
       }
+      cnt += __popc(hm);
+      if (cnt >= 4) return 4;
     }
-#pragma unroll
-    for (int f = 0; f < 6; f++) cnt += __popc(hm[f]);
-    if (cnt >= 4) return 4;
   }
   return cnt;
 }
