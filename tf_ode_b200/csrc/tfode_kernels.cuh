@@ -393,7 +393,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       for (int sw_i = 0; sw_i < nsw; sw_i++) {
         unsigned mrem = mask32;
         const unsigned short* qp = qp0;
-#pragma unroll 2
+#pragma unroll 4
         for (int t = 0; t < T - 1; t++) {
           const bool fire = (mrem & 1u) != 0u;
           qp += fire ? 1 : 0;
