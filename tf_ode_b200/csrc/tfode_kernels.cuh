@@ -249,6 +249,53 @@ __device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const f
 __device__ __forceinline__ int first_body_of_group(int g) { return g == 0 ? 0 : (g == 1 ? 4 : (g == 2 ? 5 : (g == 3 ? 10 : 11))); }
 
 constexpr int PGS_WARPS = ENVS_PER_CTA / 2;
+static_assert(PGS_WARPS <= 15, "one named barrier per warp pair");
+
+// Named barrier over 64 threads: sweep warp p and its helper warp PGS_WARPS + p (barrier 0 stays with __syncthreads).
+__device__ __forceinline__ void pair_barrier(int p) { asm volatile("bar.sync %0, 64;" ::"r"(1 + p) : "memory"); }
+
+// The island's order array after reorder r.  ODE shuffles the same array again at every 8th sweep; here the permutations of
+// reorders 0, 1 and 2 live in three buffers so that they can be prepared ahead of the sweeps that use them: r = 0 in
+// S.order (shuffled by the environment's own warp before the CTA barrier), r = 1 and r >= 2 in bytes 0 and 1 of the rows'
+// header slots (RS_HDR is dead once the order is built), written by the pair's helper warp while the sweeps of block 0 run.
+__device__ __forceinline__ unsigned char* ord_buffer(WarpSm& S, int off, int r, int& stride) {
+  if (r == 0) { stride = 1; return S.order + off; }
+  stride = (int)sizeof(S.rowS[0]);
+  return reinterpret_cast<unsigned char*>(&S.rowS[off][RS_HDR]) + (r == 1 ? 0 : 1);
+}
+// RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt on this island's slice of the environment's stream (one lane).
+// The draw of the next swap (LCG step, bit folds, reciprocal-multiply modulo) overlaps the shared-memory round trip of this one.
+__device__ __forceinline__ void fy_shuffle(unsigned char* o, int stride, int m, uint32_t seed0, int base, int r) {
+  uint32_t sd = lcg_jump(seed0, (uint32_t)(base + r * (m - 1)));
+  int sw = lcg_randint(sd, 2u);
+  for (int q = 1; q < m; q++) {
+    const int sw_next = lcg_randint_magic(sd, (uint32_t)(q + 2), c_fy_magic.v[q + 2]);
+    const unsigned char x = o[q * stride], y = o[sw * stride];
+    o[q * stride] = y; o[sw * stride] = x;
+    sw = sw_next;
+  }
+}
+// Helper warp of pair p: the permutations of reorders 1 and 2 for the pair's two environments, then the pair barrier.
+__device__ void pgs_helper(WarpSm* sm, int pgs_iters, int p, int lane) {
+  const int e = 2 * p + (lane >> 4), b = lane & 15;
+  WarpSm& S = sm[e];
+  if (S.pgs_on != 0 && b < NB) {
+    const int g = body_group(b), L = S.isl_lab[g];
+    const int off = S.isl_off[L], m = S.isl_m[L], base = S.isl_base[L];
+    if (b == first_body_of_group(g) && L == g && m > 0) {
+      int sa, sb, sc;
+      unsigned char* A = ord_buffer(S, off, 0, sa); unsigned char* B = ord_buffer(S, off, 1, sb); unsigned char* C = ord_buffer(S, off, 2, sc);
+      for (int k = 0; k < m; k++) B[k * sb] = A[k * sa];
+      if (m > 1) fy_shuffle(B, sb, m, S.c.lcg_seed, base, 1);
+      if (pgs_iters > 16) {
+        for (int k = 0; k < m; k++) C[k * sc] = B[k * sb];
+        if (m > 1) fy_shuffle(C, sc, m, S.c.lcg_seed, base, 2);
+      }
+    }
+  }
+  __syncwarp();
+  pair_barrier(p);
+}
 
 __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   const int e = 2 * wid + (lane >> 4), b = lane & 15;
@@ -271,7 +318,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     iI[0] = ia.x; iI[1] = ia.y; iI[2] = ia.z; iI[3] = ia.w; iI[4] = ib.x; iI[5] = ib.y; invM = ib.z;
     seed0 = S.c.lcg_seed;
   }
-  unsigned char* const ord = S.order + off;
+  int ostride = 1;
+  unsigned char* ord = S.order + off;   // reorder 0: shuffled by the environment's own warp before the CTA barrier
   unsigned short* const queue = reinterpret_cast<unsigned short*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
   static_assert(2 * MAXROWS * sizeof(unsigned short) <= sizeof(float) * MAXC * 8, "queues alias the contact list");
   PG_DECL
@@ -293,19 +341,16 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   const int dummy_ent = (b << 8) | BR_SOLO;   // idle slot: row 0, one-body, partner = self, never fires
   for (int it0 = 0; it0 < pgs_iters; it0 += 8) {
     const int nsw = min(8, pgs_iters - it0);   // sweeps until the next reorder
-    {  // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt, this island's slice of the env's stream
+    {  // RANDOMLY_REORDER_CONSTRAINTS: the permutations of reorders 0..2 are ready in their buffers (ord_buffer); later ones
+       // (pgs_iters > 24) are shuffled here, in place on the last buffer
       PG_MARK(3)
-      if (leader && m > 1) {
-        uint32_t sd = lcg_jump(seed0, (uint32_t)(base + (it0 >> 3) * (m - 1)));
-        int sw = lcg_randint(sd, 2u);
-        for (int q = 1; q < m; q++) {   // the draw of the next swap (LCG step, bit folds, modulo) overlaps the shared-memory round trip of this one
-          const int sw_next = lcg_randint_magic(sd, (uint32_t)(q + 2), c_fy_magic.v[q + 2]);
-          const unsigned char x = ord[q], y = ord[sw];
-          ord[q] = y; ord[sw] = x;
-          sw = sw_next;
-        }
+      const int rr = it0 >> 3;
+      if (rr == 1) pair_barrier(wid);   // the helper warp has finished both of its permutations long before
+      if (rr >= 1) ord = ord_buffer(S, off, rr, ostride);
+      if (rr >= 3) {
+        if (leader && m > 1) fy_shuffle(ord, ostride, m, seed0, base, rr);
+        __syncwarp();
       }
-      __syncwarp();
       PG_MARK(1)
       // Queue fill.  Every row carries its two pre-decoded entries (RS_ENT); an entry's partner field names the OTHER body, so
       // this lane's body is body 1 of the row iff the second entry's partner is b, body 2 iff the first entry's partner is b
@@ -313,12 +358,12 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       unsigned short* qw = myq;
       int k = 0;
       for (; k + 4 <= m; k += 4) {
-        const int r0 = ord[k], r1 = ord[k + 1], r2 = ord[k + 2], r3 = ord[k + 3];
+        const int r0 = ord[k * ostride], r1 = ord[(k + 1) * ostride], r2 = ord[(k + 2) * ostride], r3 = ord[(k + 3) * ostride];
         const int p0 = __float_as_int(S.rowS[r0][RS_ENT]), p1 = __float_as_int(S.rowS[r1][RS_ENT]);
         const int p2 = __float_as_int(S.rowS[r2][RS_ENT]), p3 = __float_as_int(S.rowS[r3][RS_ENT]);
         pgs_push(qw, p0, b); pgs_push(qw, p1, b); pgs_push(qw, p2, b); pgs_push(qw, p3, b);
       }
-      for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k]][RS_ENT]), b);
+      for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k * ostride]][RS_ENT]), b);
       __syncwarp();
     }
     // Static firing schedule.  Which lock-step a row fires at depends only on the queues (a row fires when it heads the
@@ -968,6 +1013,12 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         }
       }
       __syncwarp();
+      if (lane < NB) {   // reorder 0 of every island (ODE shuffles before the first sweep), one leader lane per island
+        const int g = body_group(lane), L = S.isl_lab[g];
+        const int m_i = S.isl_m[L];
+        if (lane == first_body_of_group(g) && L == g && m_i > 1) fy_shuffle(S.order + S.isl_off[L], 1, m_i, S.c.lcg_seed, S.isl_base[L], 0);
+      }
+      __syncwarp();
 
       if (lane < NB) {  // btmp becomes fc: the sweeps start from zero constraint acceleration
 #pragma unroll
@@ -981,6 +1032,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
 
     // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
     if (wid < PGS_WARPS) pgs_bodylane(sm, cfg.pgs_iters, wid, lane);
+    else if (cfg.pgs_iters > 8) pgs_helper(sm, cfg.pgs_iters, wid - PGS_WARPS, lane);   // permutations of the later reorders, off the sweeps' path
     PT_MARK(3)
     __syncthreads();
     PT_MARK(4)
