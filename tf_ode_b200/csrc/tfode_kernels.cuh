@@ -275,26 +275,102 @@ __device__ __forceinline__ void fy_shuffle(unsigned char* o, int stride, int m, 
     sw = sw_next;
   }
 }
-// Helper warp of pair p: the permutations of reorders 1 and 2 for the pair's two environments, then the pair barrier.
+// Scratch of the sweep phase.  The body tables (bR, bvel: published poses and velocities) are dead between the row build and
+// the re-publication after the integration, so the second queue buffer and the schedule hand-over live there.
+//   queue buffer 0: the contact list (dead once the rows are built)      -> reorders 0, 2, 3, ...
+//   queue buffer 1: bR                                                   -> reorder 1
+//   hand-over     : bvel as unsigned[2][17]: fire mask of body lane b, [16] = lock-steps per sweep, for reorders 1 and 2
+__device__ __forceinline__ unsigned short* pgs_queue_buffer(WarpSm& S, int which) {
+  static_assert(2 * MAXROWS * sizeof(unsigned short) <= sizeof(float) * MAXC * 8, "queues alias the contact list");
+  static_assert(2 * MAXROWS * sizeof(unsigned short) <= sizeof(float) * NB * 12, "second queue buffer aliases bR");
+  static_assert(2 * 17 * sizeof(unsigned) <= sizeof(float) * NB * 8, "schedule hand-over aliases bvel");
+  return which ? reinterpret_cast<unsigned short*>(&S.bR[0][0]) : reinterpret_cast<unsigned short*>(&S.cont[0][0]);
+}
+__device__ __forceinline__ unsigned* pgs_handover(WarpSm& S, int r) { return reinterpret_cast<unsigned*>(&S.bvel[0][0]) + (r - 1) * 17; }
+
+// One reorder's queue fill + static firing schedule for body lane b (all 32 lanes of the warp take part in the shuffles).
+//  * fill: every row carries its two pre-decoded entries (RS_ENT); an entry's partner field names the OTHER body, so this
+//    lane's body is body 1 of the row iff the second entry's partner is b, body 2 iff the first entry's partner is b (a
+//    one-body row names its own body in both, and its lane takes the first).  Branch-free, four rows per round.
+//  * schedule: which lock-step a row fires at depends only on the queues (a row fires when it heads the queues of both of its
+//    bodies), not on any value, so the integer part of the lock-step loop is run once per reorder: bit t of `mask0` = this
+//    lane relaxes its next queue entry at lock-step t; T = lock-steps per sweep (warp-uniform).
+__device__ __forceinline__ void pgs_fill_sched(const WarpSm& S, const unsigned char* ord, int ostride, int m, int b, int hbase,
+                                               unsigned short* myq, int qn, int dummy_ent, unsigned long long& mask0, int& T) {
+  unsigned short* qw = myq;
+  int k = 0;
+  for (; k + 4 <= m; k += 4) {
+    const int r0 = ord[k * ostride], r1 = ord[(k + 1) * ostride], r2 = ord[(k + 2) * ostride], r3 = ord[(k + 3) * ostride];
+    const int p0 = __float_as_int(S.rowS[r0][RS_ENT]), p1 = __float_as_int(S.rowS[r1][RS_ENT]);
+    const int p2 = __float_as_int(S.rowS[r2][RS_ENT]), p3 = __float_as_int(S.rowS[r3][RS_ENT]);
+    pgs_push(qw, p0, b); pgs_push(qw, p1, b); pgs_push(qw, p2, b); pgs_push(qw, p3, b);
+  }
+  for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k * ostride]][RS_ENT]), b);
+  __syncwarp();
+  mask0 = 0ull; T = 0;
+  int cur = 0, ent = qn > 0 ? (int)myq[0] : dummy_ent;
+  while (__any_sync(FULLMASK, cur < qn)) {
+    const bool have = cur < qn;
+    const int myrow = have ? (ent & 127) : -1;
+    const int prow = __shfl_sync(FULLMASK, myrow, hbase | ((ent >> 8) & 15));
+    if (have && ((ent & BR_SOLO) || prow == myrow)) {
+      if (T < 64) mask0 |= 1ull << T;
+      cur++;
+      if (cur < qn) ent = myq[cur];
+    }
+    T++;
+  }
+}
+// rows of body b in its island (does not depend on the permutation) and the start of its queue inside a queue buffer
+__device__ __forceinline__ void pgs_queue_extent(const WarpSm& S, const unsigned char* ordA, int m, int b, int& qn, int& qoff) {
+  qn = 0;
+  for (int k = 0; k < m; k++) {
+    const int pk = __float_as_int(S.rowS[ordA[k]][RS_ENT]);
+    if (((pk >> 24) & 15) == b || ((pk >> 8) & 15) == b) qn++;
+  }
+  int incl = qn;
+#pragma unroll
+  for (int d = 1; d < 16; d <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, d, 16); if (b >= d) incl += t; }
+  qoff = incl - qn;
+}
+
+// Helper warp of pair p: everything reorders 1 and 2 need that does not depend on the solve -- permutation, queues, firing
+// schedule -- for the pair's two environments, handed to the sweep warp at two meetings of the pair's named barrier.
 __device__ void pgs_helper(WarpSm* sm, int pgs_iters, int p, int lane) {
-  const int e = 2 * p + (lane >> 4), b = lane & 15;
+  const int e = 2 * p + (lane >> 4), b = lane & 15, hbase = lane & 16;
   WarpSm& S = sm[e];
-  if (S.pgs_on != 0 && b < NB) {
+  const bool on = S.pgs_on != 0 && b < NB;
+  int off = 0, m = 0, base = 0; bool leader = false;
+  if (on) {
     const int g = body_group(b), L = S.isl_lab[g];
-    const int off = S.isl_off[L], m = S.isl_m[L], base = S.isl_base[L];
-    if (b == first_body_of_group(g) && L == g && m > 0) {
-      int sa, sb, sc;
-      unsigned char* A = ord_buffer(S, off, 0, sa); unsigned char* B = ord_buffer(S, off, 1, sb); unsigned char* C = ord_buffer(S, off, 2, sc);
-      for (int k = 0; k < m; k++) B[k * sb] = A[k * sa];
-      if (m > 1) fy_shuffle(B, sb, m, S.c.lcg_seed, base, 1);
-      if (pgs_iters > 16) {
-        for (int k = 0; k < m; k++) C[k * sc] = B[k * sb];
-        if (m > 1) fy_shuffle(C, sc, m, S.c.lcg_seed, base, 2);
-      }
+    off = S.isl_off[L]; m = S.isl_m[L]; base = S.isl_base[L];
+    leader = (b == first_body_of_group(g)) && (L == g);
+  }
+  int sa, sb, sc;
+  unsigned char* A = ord_buffer(S, off, 0, sa); unsigned char* B = ord_buffer(S, off, 1, sb); unsigned char* C = ord_buffer(S, off, 2, sc);
+  if (leader && m > 0) {
+    for (int k = 0; k < m; k++) B[k * sb] = A[k * sa];
+    if (m > 1) fy_shuffle(B, sb, m, S.c.lcg_seed, base, 1);
+    if (pgs_iters > 16) {
+      for (int k = 0; k < m; k++) C[k * sc] = B[k * sb];
+      if (m > 1) fy_shuffle(C, sc, m, S.c.lcg_seed, base, 2);
     }
   }
+  int qn, qoff;
+  pgs_queue_extent(S, A, m, b, qn, qoff);
   __syncwarp();
-  pair_barrier(p);
+  const int dummy_ent = (b << 8) | BR_SOLO;
+  unsigned long long mask0; int T;
+  pgs_fill_sched(S, B, sb, m, b, hbase, pgs_queue_buffer(S, 1) + qoff, qn, dummy_ent, mask0, T);
+  if (on) { unsigned* h = pgs_handover(S, 1); h[b] = (unsigned)mask0; if (b == 0) h[16] = (unsigned)T; }
+  __syncwarp();
+  pair_barrier(p);   // reorder 1 is ready; the sweep warp has left queue buffer 0
+  if (pgs_iters > 16) {
+    pgs_fill_sched(S, C, sc, m, b, hbase, pgs_queue_buffer(S, 0) + qoff, qn, dummy_ent, mask0, T);
+    if (on) { unsigned* h = pgs_handover(S, 2); h[b] = (unsigned)mask0; if (b == 0) h[16] = (unsigned)T; }
+    __syncwarp();
+    pair_barrier(p);   // reorder 2 is ready
+  }
 }
 
 __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
@@ -320,68 +396,38 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   }
   int ostride = 1;
   unsigned char* ord = S.order + off;   // reorder 0: shuffled by the environment's own warp before the CTA barrier
-  unsigned short* const queue = reinterpret_cast<unsigned short*>(&S.cont[0][0]);  // the contact list is dead once the rows are built
-  static_assert(2 * MAXROWS * sizeof(unsigned short) <= sizeof(float) * MAXC * 8, "queues alias the contact list");
   PG_DECL
 #ifdef TFODE_PHASE_TIMING
   int nsteps = 0;
 #endif
-  // rows per body (does not depend on the permutation) -> start of each body's queue
-  int qn = 0;
-  for (int k = 0; k < m; k++) {
-    const int pk = __float_as_int(S.rowS[ord[k]][RS_ENT]);
-    if (((pk >> 24) & 15) == b || ((pk >> 8) & 15) == b) qn++;
-  }
-  int incl = qn;
-#pragma unroll
-  for (int d = 1; d < 16; d <<= 1) { const int t = __shfl_up_sync(FULLMASK, incl, d, 16); if (b >= d) incl += t; }
-  unsigned short* const myq = queue + (incl - qn);
+  int qn, qoff;
+  pgs_queue_extent(S, ord, m, b, qn, qoff);
+  unsigned short* myq = pgs_queue_buffer(S, 0) + qoff;
 
   PG_MARK(0)
   const int dummy_ent = (b << 8) | BR_SOLO;   // idle slot: row 0, one-body, partner = self, never fires
   for (int it0 = 0; it0 < pgs_iters; it0 += 8) {
     const int nsw = min(8, pgs_iters - it0);   // sweeps until the next reorder
+    unsigned long long mask0 = 0ull; int T = 0;
     {  // RANDOMLY_REORDER_CONSTRAINTS: the permutations of reorders 0..2 are ready in their buffers (ord_buffer); later ones
        // (pgs_iters > 24) are shuffled here, in place on the last buffer
       PG_MARK(3)
       const int rr = it0 >> 3;
-      if (rr == 1) pair_barrier(wid);   // the helper warp has finished both of its permutations long before
-      if (rr >= 1) ord = ord_buffer(S, off, rr, ostride);
-      if (rr >= 3) {
-        if (leader && m > 1) fy_shuffle(ord, ostride, m, seed0, base, rr);
-        __syncwarp();
-      }
-      PG_MARK(1)
-      // Queue fill.  Every row carries its two pre-decoded entries (RS_ENT); an entry's partner field names the OTHER body, so
-      // this lane's body is body 1 of the row iff the second entry's partner is b, body 2 iff the first entry's partner is b
-      // (a one-body row names its own body in both, and its lane takes the first).  Branch-free, four rows per round.
-      unsigned short* qw = myq;
-      int k = 0;
-      for (; k + 4 <= m; k += 4) {
-        const int r0 = ord[k * ostride], r1 = ord[(k + 1) * ostride], r2 = ord[(k + 2) * ostride], r3 = ord[(k + 3) * ostride];
-        const int p0 = __float_as_int(S.rowS[r0][RS_ENT]), p1 = __float_as_int(S.rowS[r1][RS_ENT]);
-        const int p2 = __float_as_int(S.rowS[r2][RS_ENT]), p3 = __float_as_int(S.rowS[r3][RS_ENT]);
-        pgs_push(qw, p0, b); pgs_push(qw, p1, b); pgs_push(qw, p2, b); pgs_push(qw, p3, b);
-      }
-      for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k * ostride]][RS_ENT]), b);
-      __syncwarp();
-    }
-    // Static firing schedule.  Which lock-step a row fires at depends only on the queues (a row fires when it heads the
-    // queues of both of its bodies), not on any value, so the integer part of the lock-step loop is run once per
-    // reorder: bit t of `mask0` = this lane relaxes its next queue entry at lock-step t; T = lock-steps per sweep.
-    unsigned long long mask0 = 0ull; int T = 0;
-    {
-      int cur = 0, ent = qn > 0 ? (int)myq[0] : dummy_ent;
-      while (__any_sync(FULLMASK, cur < qn)) {
-        const bool have = cur < qn;
-        const int myrow = have ? (ent & 127) : -1;
-        const int prow = __shfl_sync(FULLMASK, myrow, hbase | ((ent >> 8) & 15));
-        if (have && ((ent & BR_SOLO) || prow == myrow)) {
-          if (T < 64) mask0 |= 1ull << T;
-          cur++;
-          if (cur < qn) ent = myq[cur];
+      if (rr == 1 || rr == 2) {
+        pair_barrier(wid);   // the helper warp finished this reorder long ago (permutation, queues, schedule)
+        myq = pgs_queue_buffer(S, rr == 1 ? 1 : 0) + qoff;
+        const unsigned* h = pgs_handover(S, rr);
+        mask0 = on ? (unsigned long long)h[b] : 0ull;
+        T = __reduce_max_sync(FULLMASK, on ? (int)h[16] : 0);
+      } else {
+        if (rr >= 3) {
+          ord = ord_buffer(S, off, rr, ostride);
+          if (leader && m > 1) fy_shuffle(ord, ostride, m, seed0, base, rr);
+          __syncwarp();
+          myq = pgs_queue_buffer(S, 0) + qoff;
         }
-        T++;
+        PG_MARK(1)
+        pgs_fill_sched(S, ord, ostride, m, b, hbase, myq, qn, dummy_ent, mask0, T);
       }
     }
     PG_MARK(2)
