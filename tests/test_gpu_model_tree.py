@@ -121,3 +121,18 @@ def test_reference_terrain_batch_contact_counts_bit_exact():
     for e in range(0, n, 9):
         assert_states_equal(g.get_state(e), o.get_state(e), 10, True, "env %d" % e)
     g.close(); o.close()
+
+
+@pytest.mark.parametrize("iters", [5, 8, 12, 16, 17, 30])
+def test_other_sweep_counts_are_bit_exact(iters):
+    """pgs_iters decides how many reorders a step has (one per 8 sweeps): none beyond the first (<= 8, no helper warp), one
+    (9..16), two (17..24), and in-place shuffles past the third (> 24)."""
+    hm = reference_heightmap("rock_groove")
+    for kw in (dict(), dict(heightfield=(hm, 3.0, 3.0, (1.0, 0.0, -0.3)))):
+        mk = lambda: make_config(abi.PRESET_MT_RANDOM, 4, pgs_iters=iters, speedf=0.4, **kw)  # noqa: E731
+        g, o = RoverBatch(mk()), oracle_lib.Oracle(mk(), "float")
+        for k in range(30):
+            g.step(50); o.step(50)
+            for e in range(4):
+                assert_states_equal(g.get_state(e), o.get_state(e), nbodies(g.cfg), True, "iters %d step %d env %d" % (iters, (k + 1) * 50, e))
+        g.close(); o.close()
