@@ -116,63 +116,9 @@ __device__ void get_state17(const WarpSm& S, float* s) {
 //                                         THE STEP KERNEL
 // One CTA = ENVS_PER_CTA environments.  Collision, row construction, integration and the rover's control
 // code run with one warp per environment (lane = body / geom / joint / row).  The Gauss-Seidel sweeps,
-// which are sequential inside a constraint island, run "packed": warp 0 of the CTA gives every island of
-// every environment its own lane (4 lanes per environment), so a sweep instruction serves up to 32 islands.
+// which are sequential inside a constraint island, run in "body-lane" form on half of the CTA's warps (a
+// half-warp per environment, lane = rigid body); the other warps prepare the later reorders (pgs_helper).
 // ================================================================================================
-
-// One row relaxation of SOR_LCP (quickstep.cpp) for the island this lane owns; everything in shared memory.
-// The row loop is software-pipelined by hand: the only loop-carried dependence of a sweep is the constraint
-// acceleration fc of the row's two bodies (and lambda of a friction row's normal row), so everything that is
-// constant during the sweeps (J, rhs, Ad, limits, header of the NEXT row; inverse inertia of the CURRENT row's
-// bodies) is requested at the top of the iteration, ahead of the stores of the current row, and one shared-memory
-// round trip per row remains on the critical path instead of four.
-struct RowStatic { float4 s0; float hi; int hdr; float4 j0, j1, j2; };
-__device__ __forceinline__ void pgs_load_static(const WarpSm& S, int row, RowStatic& r) {
-  r.s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);   // rhs Ad Adcfm lo
-  r.hi = S.rowS[row][RS_HI];
-  r.hdr = __float_as_int(S.rowS[row][RS_HDR]);
-  const float4* Jp = reinterpret_cast<const float4*>(&S.rowJ[row][0]);
-  r.j0 = Jp[0]; r.j1 = Jp[1]; r.j2 = Jp[2];
-}
-__device__ __forceinline__ void pgs_row_update(WarpSm& S, int row, const RowStatic& r, bool act) {
-  const int b1 = r.hdr & 15, b2r = (r.hdr >> 4) & 15, fidx = (r.hdr >> 8) & 255;
-  const bool has2 = b2r < NB;
-  const int b2 = has2 ? b2r : b1;
-  // constant during the sweeps: world inverse inertia + inverse mass of the two bodies
-  const float4 ia1 = *reinterpret_cast<const float4*>(&S.binvI[b1][0]); const float4 ib1 = *reinterpret_cast<const float4*>(&S.binvI[b1][4]);
-  const float4 ia2 = *reinterpret_cast<const float4*>(&S.binvI[b2][0]); const float4 ib2 = *reinterpret_cast<const float4*>(&S.binvI[b2][4]);
-  // loop-carried: fc of the two bodies, lambda of this row and of the normal row of a friction row
-  const float4 fa1 = *reinterpret_cast<const float4*>(&S.btmp[b1][0]); const float2 fb1 = *reinterpret_cast<const float2*>(&S.btmp[b1][4]);
-  const float4 fa2 = *reinterpret_cast<const float4*>(&S.btmp[b2][0]); const float2 fb2 = *reinterpret_cast<const float2*>(&S.btmp[b2][4]);
-  const float lam = S.rowS[row][RS_LAM];
-  const float lamf = S.rowS[(act && fidx != 255) ? fidx : row][RS_LAM];  // (idle lanes hold an arbitrary header)
-  const float J[12] = {r.j0.x, r.j0.y, r.j0.z, r.j0.w, r.j1.x, r.j1.y, r.j1.z, r.j1.w, r.j2.x, r.j2.y, r.j2.z, r.j2.w};
-  const float f1[6] = {fa1.x, fa1.y, fa1.z, fa1.w, fb1.x, fb1.y}, f2[6] = {fa2.x, fa2.y, fa2.z, fa2.w, fb2.x, fb2.y};
-  // M^-1 J^T of the row (independent of fc: overlaps the loads above)
-  const float a1x = tfn::dot3(ia1.x, ia1.y, ia1.z, J[3], J[4], J[5]), a1y = tfn::dot3(ia1.y, ia1.w, ib1.x, J[3], J[4], J[5]), a1z = tfn::dot3(ia1.z, ib1.x, ib1.y, J[3], J[4], J[5]);
-  const float a2x = tfn::dot3(ia2.x, ia2.y, ia2.z, J[9], J[10], J[11]), a2y = tfn::dot3(ia2.y, ia2.w, ib2.x, J[9], J[10], J[11]), a2z = tfn::dot3(ia2.z, ib2.x, ib2.y, J[9], J[10], J[11]);
-  float sum = tfn::dot6(J, f1);
-  const float sum2 = sum + tfn::dot6(J + 6, f2);
-  if (has2) sum = sum2;
-  float lo = r.s0.w, hi = r.hi;
-  if (fidx != 255) { hi = fabsf(hi * lamf); lo = -hi; }
-  float delta = tfn::fma(r.s0.y, r.s0.x - sum, -(lam * r.s0.z));
-  float nl = lam + delta;
-  if (nl < lo) { delta = lo - lam; nl = lo; }
-  else if (nl > hi) { delta = hi - lam; nl = hi; }
-  const float dm1 = delta * ib1.z, dm2 = delta * ib2.z;
-  float4 o; float2 o2;
-  o.x = tfn::fma(dm1, J[0], f1[0]); o.y = tfn::fma(dm1, J[1], f1[1]); o.z = tfn::fma(dm1, J[2], f1[2]);
-  o.w = tfn::fma(delta, a1x, f1[3]); o2.x = tfn::fma(delta, a1y, f1[4]); o2.y = tfn::fma(delta, a1z, f1[5]);
-  float4 p; float2 p2;
-  p.x = tfn::fma(dm2, J[6], f2[0]); p.y = tfn::fma(dm2, J[7], f2[1]); p.z = tfn::fma(dm2, J[8], f2[2]);
-  p.w = tfn::fma(delta, a2x, f2[3]); p2.x = tfn::fma(delta, a2y, f2[4]); p2.y = tfn::fma(delta, a2z, f2[5]);
-  if (act) {
-    S.rowS[row][RS_LAM] = nl;
-    *reinterpret_cast<float4*>(&S.btmp[b1][0]) = o; *reinterpret_cast<float2*>(&S.btmp[b1][4]) = o2;
-    if (has2) { *reinterpret_cast<float4*>(&S.btmp[b2][0]) = p; *reinterpret_cast<float2*>(&S.btmp[b2][4]) = p2; }
-  }
-}
 
 // Developer-only phase timers (build with -DTFODE_PHASE_TIMING: tools/phase_timing.py); never compiled into the product library.
 #ifdef TFODE_PHASE_TIMING
