@@ -1005,10 +1005,35 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         }
       }
       __syncwarp();
-      if (lane < NB) {   // reorder 0 of every island (ODE shuffles before the first sweep), one leader lane per island
-        const int g = body_group(lane), L = S.isl_lab[g];
-        const int m_i = S.isl_m[L];
-        if (lane == first_body_of_group(g) && L == g && m_i > 1) fy_shuffle(S.order + S.isl_off[L], 1, m_i, S.c.lcg_seed, S.isl_base[L], 0);
+      // Reorder 0 of every island (ODE shuffles before the first sweep).  The draws depend on the stream position only, so
+      // all 32 lanes compute them at once (LCG jump-ahead to each draw's position) into the dead contact list; the swap
+      // chain itself, the sequential part of Fisher-Yates, then runs with one leader lane per island.
+      {
+        unsigned char* dr = reinterpret_cast<unsigned char*>(&S.cont[0][0]);
+        const uint32_t seed_now = S.c.lcg_seed;
+#pragma unroll 1
+        for (int L = 0; L < NISL; L++) {
+          const int m_l = S.isl_m[L], off_l = S.isl_off[L], base_l = S.isl_base[L];
+          for (int q = 1 + lane; q < m_l; q += 32) {
+            uint32_t sd = lcg_jump(seed_now, (uint32_t)(base_l + q - 1));
+            dr[off_l + q] = (unsigned char)lcg_randint_magic(sd, (uint32_t)(q + 1), c_fy_magic.v[q + 1]);
+          }
+        }
+        __syncwarp();
+        if (lane < NB) {
+          const int g = body_group(lane), L = S.isl_lab[g];
+          const int m_i = S.isl_m[L];
+          if (lane == first_body_of_group(g) && L == g && m_i > 1) {
+            unsigned char* o = S.order + S.isl_off[L]; const unsigned char* d = dr + S.isl_off[L];
+            int sw = d[1];
+            for (int q = 1; q < m_i; q++) {
+              const int sw_next = d[q + 1 < m_i ? q + 1 : q];
+              const unsigned char x = o[q], y = o[sw];
+              o[q] = y; o[sw] = x;
+              sw = sw_next;
+            }
+          }
+        }
       }
       __syncwarp();
 
