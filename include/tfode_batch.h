@@ -203,6 +203,19 @@ int tfode_batch_set_speed(TfodeBatch* b, const float* speed_dev);
  * W1[17,512] b1[512] W2[512,512] b2[512] W3[512,2] b3[2]  (272 898 floats). */
 int tfode_batch_load_policy(TfodeBatch* b, const float* weights, size_t n_floats);
 
+/* TF_model<float>( actor_dir, s_dim, a_dim ) (tf_cpp_binding.cc:14-66; called with the directory written by
+ * `td3.actor.save( session_dir + '/actor' )`, scripts/rover_training_1.py:90,121, from src/rover_1_tf.cc:24):
+ * read the three Dense layers of scripts/rover_training_1.py:26-35 out of
+ * <saved_model_dir>/variables/variables.index + variables.data-XXXXX-of-YYYYY (TensorFlow tensor-bundle checkpoint:
+ * keys layer_with_weights-{0,1,2}/{kernel,bias}/.ATTRIBUTES/VARIABLE_VALUE, DT_FLOAT, little-endian) into the blob
+ * layout of tfode_batch_load_policy.  *weights_out is malloc'ed (tfode_free).  Anything else -- missing file or
+ * variable, wrong dtype or shape, compressed index blocks, checksum mismatch -- is TFODE_EINVAL with the reason in
+ * tfode_last_error(NULL).  The graph (saved_model.pb) is not read: the architecture is the reference's fixed actor.
+ * FORMAT UNPINNED (no SavedModel ships with the reference, TensorFlow absent here). */
+int tfode_savedmodel_read_actor(const char* saved_model_dir, float** weights_out, size_t* n_floats_out);
+/* The two calls above in one: what Rover_1_tf's constructor does with its `actor_path`. */
+int tfode_batch_load_policy_saved_model(TfodeBatch* b, const char* saved_model_dir);
+
 /* n x { step_function(dt,time) } of src/rover_training_1.cc:127-146 for every env:
  * speed ramp, IC activation, Environment::next_step (ode/environment.hh:127-136 with
  * dWorldQuickStep), Rover_1::next_step (src/rover_1.cc:478-503), termination test. */

@@ -248,3 +248,178 @@ def test_oracle_interaction_only_features_follow_sklearn_order(tree_oracle):
     want = np.hstack(feats) @ w[:-1] + w[-1]
     y, node = tree_oracle.model_tree_predict(0, x)
     assert (node == 1).all() and np.allclose(y, want, rtol=1e-12)
+
+
+# ---------------------------------------------------------------------------------------------------------------------- SavedModel variables
+# Writer of the TensorFlow tensor-bundle checkpoint as TensorFlow's BundleWriter lays it out (tensor_bundle.cc + lib/io/table_builder.cc:
+# sorted keys, shared-prefix compression with a restart every 16 entries, uncompressed blocks with a masked-CRC32C trailer, empty metaindex
+# block, index block, 48-byte footer).  FORMAT UNPINNED: restated from the published format, no TensorFlow-written file exists on this box.
+def _crc32c(data):
+    tbl = _crc32c.tbl
+    if tbl is None:
+        tbl = []
+        for i in range(256):
+            c = i
+            for _ in range(8):
+                c = (c >> 1) ^ (0x82F63B78 if c & 1 else 0)
+            tbl.append(c)
+        _crc32c.tbl = tbl
+    c = 0xFFFFFFFF
+    for b in data:
+        c = tbl[(c ^ b) & 0xFF] ^ (c >> 8)
+    return c ^ 0xFFFFFFFF
+
+
+_crc32c.tbl = None
+
+
+def _mask(crc):
+    return ((((crc >> 15) | (crc << 17)) & 0xFFFFFFFF) + 0xA282EAD8) & 0xFFFFFFFF
+
+
+def _varint(v):
+    out = bytearray()
+    while True:
+        b = v & 0x7F
+        v >>= 7
+        out.append(b | (0x80 if v else 0))
+        if not v:
+            return bytes(out)
+
+
+def _table_block(entries, restart_interval=16):
+    body, restarts, last = bytearray(), [], b""
+    for i, (k, v) in enumerate(entries):
+        shared = 0
+        if i % restart_interval == 0:
+            restarts.append(len(body))
+        else:
+            while shared < min(len(k), len(last)) and k[shared] == last[shared]:
+                shared += 1
+        body += _varint(shared) + _varint(len(k) - shared) + _varint(len(v)) + k[shared:] + v
+        last = k
+    if not restarts:
+        restarts = [0]
+    for r in restarts:
+        body += struct.pack("<I", r)
+    return bytes(body + struct.pack("<I", len(restarts)))
+
+
+def _entry_proto(dtype, shape, shard, offset, size, crc):
+    dims = b"".join(b"\x12" + _varint(len(d)) + d for d in (b"\x08" + _varint(s) for s in shape))
+    return (b"\x08" + _varint(dtype) + b"\x12" + _varint(len(dims)) + dims + (b"\x18" + _varint(shard) if shard else b"")
+            + (b"\x20" + _varint(offset) if offset else b"") + b"\x28" + _varint(size) + b"\x35" + struct.pack("<I", crc))
+
+
+def write_bundle(prefix, tensors, num_shards=1, entries_per_block=1000, compression=0, corrupt=None, extra_entries=()):
+    """tensors: {key: (np array, dtype enum)}; tensor i goes to shard i % num_shards."""
+    data = [bytearray() for _ in range(num_shards)]
+    entries = [(b"", b"\x08" + _varint(num_shards) + b"\x1a\x02\x08\x01")]   # BundleHeaderProto: num_shards, version { producer: 1 }
+    for i, key in enumerate(sorted(tensors)):
+        arr, dtype = tensors[key]
+        raw = np.ascontiguousarray(arr).tobytes()
+        sh = i % num_shards
+        off = len(data[sh])
+        data[sh] += raw
+        crc = _mask(_crc32c(raw))
+        if corrupt == key:
+            crc ^= 1
+        entries.append((key.encode(), _entry_proto(dtype, arr.shape, sh, off, len(raw), crc)))
+    entries += list(extra_entries)
+    entries.sort()
+    out, index = bytearray(), []
+
+    def emit(block):
+        handle = _varint(len(out)) + _varint(len(block))
+        out.extend(block + bytes([compression]) + struct.pack("<I", _mask(_crc32c(block + bytes([compression])))))
+        return handle
+
+    for k in range(0, len(entries), entries_per_block):
+        chunk = entries[k:k + entries_per_block]
+        index.append((chunk[-1][0] + b"\x00", emit(_table_block(chunk))))     # any separator >= the block's last key
+    meta = emit(_table_block([]))
+    idx = emit(_table_block(index, restart_interval=1))
+    foot = meta + idx
+    out.extend(foot + b"\x00" * (40 - len(foot)) + struct.pack("<Q", 0xDB4775248B80FB57))
+    os.makedirs(os.path.dirname(prefix), exist_ok=True)
+    with open(prefix + ".index", "wb") as f:
+        f.write(out)
+    for s in range(num_shards):
+        with open(prefix + ".data-%05d-of-%05d" % (s, num_shards), "wb") as f:
+            f.write(data[s])
+
+
+def _actor_tensors(seed=3, dims=(17, 512, 512, 2)):
+    rng = np.random.default_rng(seed)
+    t, blob = {}, []
+    for l in range(len(dims) - 1):
+        w = rng.standard_normal((dims[l], dims[l + 1])).astype(np.float32)
+        b = rng.standard_normal(dims[l + 1]).astype(np.float32)
+        t["layer_with_weights-%d/kernel/.ATTRIBUTES/VARIABLE_VALUE" % l] = (w, 1)
+        t["layer_with_weights-%d/bias/.ATTRIBUTES/VARIABLE_VALUE" % l] = (b, 1)
+        blob += [w.ravel(), b.ravel()]
+    t["_CHECKPOINTABLE_OBJECT_GRAPH"] = (np.frombuffer(b"\x0a\x10object-graph-pb", dtype=np.uint8), 7)   # DT_STRING payload, skipped
+    return t, np.concatenate(blob)
+
+
+def test_crc32c_known_answers():
+    # RFC 3720 B.4 test vectors of CRC32C
+    assert _crc32c(b"123456789") == 0xE3069283
+    assert _crc32c(bytes(32)) == 0x8A9136AA
+    assert _crc32c(bytes([0xFF] * 32)) == 0x62A8AB43
+
+
+@pytest.mark.parametrize("num_shards,entries_per_block", [(1, 1000), (2, 3), (1, 1)])
+def test_saved_model_actor_round_trip(tmp_path, num_shards, entries_per_block):
+    from tf_ode_b200 import read_saved_model_actor
+    t, blob = _actor_tensors()
+    write_bundle(str(tmp_path / "actor" / "variables" / "variables"), t, num_shards, entries_per_block)
+    w = read_saved_model_actor(str(tmp_path / "actor"))
+    assert w.dtype == np.float32 and w.size == 272898
+    assert np.array_equal(w.view(np.uint32), blob.view(np.uint32))
+
+
+def test_saved_model_errors_are_loud(tmp_path):
+    from tf_ode_b200 import read_saved_model_actor
+    t, _ = _actor_tensors()
+    d = tmp_path / "a"
+    prefix = str(d / "variables" / "variables")
+    with pytest.raises(TfodeError, match="Can't open"):
+        read_saved_model_actor(str(d))
+    write_bundle(prefix, t, corrupt="layer_with_weights-1/kernel/.ATTRIBUTES/VARIABLE_VALUE")
+    with pytest.raises(TfodeError, match="CRC32C mismatch"):
+        read_saved_model_actor(str(d))
+    write_bundle(prefix, t, compression=1)
+    with pytest.raises(TfodeError, match="compressed block"):
+        read_saved_model_actor(str(d))
+    missing = {k: v for k, v in t.items() if "weights-2/bias" not in k}
+    write_bundle(prefix, missing)
+    with pytest.raises(TfodeError, match="no variable 'layer_with_weights-2/bias"):
+        read_saved_model_actor(str(d))
+    t64 = dict(t)
+    k0 = "layer_with_weights-0/kernel/.ATTRIBUTES/VARIABLE_VALUE"
+    t64[k0] = (t[k0][0].astype(np.float64), 2)
+    write_bundle(prefix, t64)
+    with pytest.raises(TfodeError, match="not DT_FLOAT"):
+        read_saved_model_actor(str(d))
+    tc, _ = _actor_tensors(dims=(19, 512, 512, 1))     # the critic of rover_training_1.py:41-52 saved in the actor's place
+    write_bundle(prefix, tc)
+    with pytest.raises(TfodeError, match=r"shape \[19,512,\] instead of \[17,512,\]"):
+        read_saved_model_actor(str(d))
+    write_bundle(prefix, t)
+    raw = bytearray(open(prefix + ".index", "rb").read())
+    raw[-1] ^= 0xFF
+    open(prefix + ".index", "wb").write(raw)
+    with pytest.raises(TfodeError, match="bad table magic"):
+        read_saved_model_actor(str(d))
+    write_bundle(prefix, t)
+    raw = bytearray(open(prefix + ".index", "rb").read())
+    raw[10] ^= 0x40
+    open(prefix + ".index", "wb").write(raw)
+    with pytest.raises(TfodeError, match="checksum mismatch"):
+        read_saved_model_actor(str(d))
+    write_bundle(prefix, t)
+    with open(prefix + ".data-00000-of-00001", "r+b") as f:
+        f.truncate(1000)
+    with pytest.raises(TfodeError, match="outside its data shard"):
+        read_saved_model_actor(str(d))

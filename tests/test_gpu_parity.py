@@ -174,6 +174,27 @@ def test_policy_infer_is_bit_exact_with_oracle_fp32_path():
     g.close(); o.close()
 
 
+def test_policy_from_saved_model_directory_equals_the_blob(tmp_path):
+    """Rover_1_tf's `actor_path` (src/rover_1_tf.cc:24): the SavedModel directory installs the same actor as its fp32 blob."""
+    from test_formats import _actor_tensors, write_bundle
+    t, blob = _actor_tensors(seed=11)
+    for k in t:
+        if t[k][1] == 1:
+            t[k][0][...] *= 0.05
+    blob = blob * np.float32(0.05)
+    write_bundle(str(tmp_path / "actor" / "variables" / "variables"), t, num_shards=2, entries_per_block=4)
+    x = torch.from_numpy(np.random.RandomState(2).rand(500, 17).astype(np.float32) * 2 - 1).cuda()
+    ya, yb = torch.zeros(500, 2, device="cuda"), torch.zeros(500, 2, device="cuda")
+    g = RoverBatch(make_config(abi.PRESET_TRAINING, 8))
+    g.load_policy_saved_model(str(tmp_path / "actor"))
+    g.policy_infer(x, ya)
+    g.load_policy(blob)
+    g.policy_infer(x, yb)
+    torch.cuda.synchronize()
+    assert torch.equal(ya, yb) and float(ya.abs().max()) > 0.01
+    g.close()
+
+
 def _bf16(a):
     """Round fp32 to bf16 (nearest even) and back, the rounding __float2bfloat16_rn applies to the MMA operands."""
     u = np.ascontiguousarray(a, np.float32).view(np.uint32).astype(np.uint64)

@@ -659,6 +659,30 @@ int tfode_heightmap_load_png(const char* path, double z_scale, float** heights_o
   return tfode_heightmap_decode_png(buf.data(), buf.size(), z_scale, heights_out, nrow_out, ncol_out);
 }
 
+int tfode_savedmodel_read_actor(const char* saved_model_dir, float** weights_out, size_t* n_floats_out) {
+  if (!saved_model_dir || !weights_out || !n_floats_out) { g_create_error = "null argument"; return TFODE_EINVAL; }
+  *weights_out = nullptr; *n_floats_out = 0;
+  try {
+    const int dims[4] = {TFODE_NOBS, TFODE_MLP_HIDDEN, TFODE_MLP_HIDDEN, TFODE_NACT};
+    const std::vector<float> w = tfode_fmt::read_saved_model_actor(saved_model_dir, dims, 3);
+    float* out = (float*)std::malloc(w.size() * sizeof(float));
+    if (!out) { g_create_error = "out of memory"; return TFODE_EINVAL; }
+    std::memcpy(out, w.data(), w.size() * sizeof(float));
+    *weights_out = out; *n_floats_out = w.size();
+  } catch (const std::exception& e) { g_create_error = e.what(); return TFODE_EINVAL; }
+  return TFODE_OK;
+}
+
+int tfode_batch_load_policy_saved_model(TfodeBatch* b, const char* saved_model_dir) {
+  if (!b) return TFODE_EINVAL;
+  float* w = nullptr; size_t n = 0;
+  const int rc = tfode_savedmodel_read_actor(saved_model_dir, &w, &n);
+  if (rc != TFODE_OK) { b->err = g_create_error; return rc; }
+  const int rc2 = tfode_batch_load_policy(b, w, n);
+  std::free(w);
+  return rc2;
+}
+
 #ifdef TFODE_PHASE_TIMING
 // developer build only: cumulative cycles per phase (collide, build, wait, pgs, wait, post), summed over CTAs (thread 0's clock)
 int tfode_debug_phase_cycles(unsigned long long* out8, int reset) {

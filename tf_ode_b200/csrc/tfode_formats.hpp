@@ -12,6 +12,17 @@
 //     sequences, comments, quoted or plain scalars) and flattens the tree in the constructor's own order: node ids are
 //     assigned depth-first, child 0 before child 1, exactly as _build_tree_recursively/_new_node do.
 //
+//   * TensorFlow SavedModel variables -- TF_model's constructor (scripts/MachineLearning/tf_cpp_binding/
+//     tf_cpp_binding.cc:14-66) hands the directory written by `td3.actor.save( session_dir + '/actor' )`
+//     (scripts/rover_training_1.py:90,121) to TF_LoadSessionFromSavedModel.  TensorFlow is not part of this engine:
+//     read_saved_model_actor() reads the checkpoint inside that directory directly -- `variables/variables.index`
+//     (a LevelDB-format sorted table, uncompressed blocks, key -> BundleEntryProto) and the
+//     `variables/variables.data-XXXXX-of-YYYYY` shards -- and returns the three Dense layers of
+//     scripts/rover_training_1.py:26-35 as the blob tfode_batch_load_policy takes.  FORMAT UNPINNED: no SavedModel
+//     ships with the reference and TensorFlow is absent on this box, so the layout is restated from TensorFlow's
+//     published tensor_bundle / table format and tested only against a writer of the same restatement
+//     (tests/test_formats.py); every deviation fails loudly (magic, compression, dtype, shape, CRC32C).
+//
 // Nothing here steps an environment; this is format plumbing for tfode_capi.cu.
 #pragma once
 #include <zlib.h>
@@ -286,6 +297,154 @@ inline int poly_feature_count(int n, int degree, bool interaction_only) {
     if (total > 100000) return -1;
   }
   return (int)total;
+}
+
+// ------------------------------------------------------------------------------------------------ SavedModel variables
+// CRC32C (Castagnoli, reflected 0x82F63B78) and TensorFlow's mask (lib/hash/crc32c.h): rot15 + 0xa282ead8.
+inline uint32_t crc32c(const unsigned char* p, size_t n) {
+  static uint32_t table[256]; static bool ready = false;
+  if (!ready) { for (uint32_t i = 0; i < 256; i++) { uint32_t c = i; for (int k = 0; k < 8; k++) c = (c >> 1) ^ (0x82F63B78u & (0u - (c & 1u))); table[i] = c; } ready = true; }
+  uint32_t c = 0xFFFFFFFFu;
+  for (size_t i = 0; i < n; i++) c = table[(c ^ p[i]) & 0xFF] ^ (c >> 8);
+  return c ^ 0xFFFFFFFFu;
+}
+inline uint32_t crc32c_mask(uint32_t crc) { return ((crc >> 15) | (crc << 17)) + 0xa282ead8u; }
+
+struct ByteCursor {
+  const unsigned char* p; const unsigned char* end;
+  uint64_t varint() {
+    uint64_t v = 0;
+    for (int shift = 0; shift < 64; shift += 7) {
+      if (p >= end) throw std::runtime_error("tensor bundle: truncated varint");
+      const unsigned char b = *p++;
+      v |= (uint64_t)(b & 0x7F) << shift;
+      if (!(b & 0x80)) return v;
+    }
+    throw std::runtime_error("tensor bundle: varint too long");
+  }
+  const unsigned char* take(size_t n) { if ((size_t)(end - p) < n) throw std::runtime_error("tensor bundle: truncated record"); const unsigned char* q = p; p += n; return q; }
+  bool done() const { return p >= end; }
+};
+inline uint32_t le32(const unsigned char* p) { return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24); }
+
+struct BundleEntry { int dtype = 0; std::vector<int64_t> shape; int shard = 0; int64_t offset = 0, size = 0; uint32_t crc = 0; bool has_crc = false, sliced = false; };
+struct Bundle { int num_shards = 1; std::map<std::string, BundleEntry> entries; };
+
+// One block of the table (handle = offset,size; the 5-byte trailer = compression type + crc follows it): calls
+// visit(key, value bytes) for every entry, undoing the shared-prefix key compression.
+template <class F>
+inline void table_block(const std::vector<unsigned char>& file, uint64_t off, uint64_t size, F&& visit) {
+  if (off + size + 5 > file.size() || size < 4) throw std::runtime_error("tensor bundle index: block handle outside the file");
+  if (file[off + size] != 0) throw std::runtime_error("tensor bundle index: compressed block (type " + std::to_string((int)file[off + size]) + "); BundleWriter writes uncompressed tables");
+  if (le32(&file[off + size + 1]) != crc32c_mask(crc32c(&file[off], size + 1))) throw std::runtime_error("tensor bundle index: block checksum mismatch");
+  const uint32_t n_restarts = le32(&file[off + size - 4]);
+  if ((uint64_t)n_restarts * 4 + 4 > size) throw std::runtime_error("tensor bundle index: bad restart array");
+  ByteCursor c{&file[off], &file[off] + size - 4 - (size_t)n_restarts * 4};
+  std::string key;
+  while (!c.done()) {
+    const uint64_t shared = c.varint(), non_shared = c.varint(), vlen = c.varint();
+    if (shared > key.size()) throw std::runtime_error("tensor bundle index: bad shared-prefix length");
+    key.resize(shared);
+    const unsigned char* k = c.take(non_shared); key.append((const char*)k, non_shared);
+    const unsigned char* v = c.take(vlen);
+    visit(key, v, (size_t)vlen);
+  }
+}
+
+inline BundleEntry parse_bundle_entry(const unsigned char* v, size_t n) {   // BundleEntryProto (tensor_bundle.proto)
+  BundleEntry e; ByteCursor c{v, v + n};
+  while (!c.done()) {
+    const uint64_t tag = c.varint(); const int field = (int)(tag >> 3), wire = (int)(tag & 7);
+    if (wire == 0) {
+      const uint64_t x = c.varint();
+      if (field == 1) e.dtype = (int)x; else if (field == 3) e.shard = (int)x; else if (field == 4) e.offset = (int64_t)x; else if (field == 5) e.size = (int64_t)x;
+    } else if (wire == 5) { const unsigned char* q = c.take(4); if (field == 6) { e.crc = le32(q); e.has_crc = true; } }
+    else if (wire == 1) c.take(8);
+    else if (wire == 2) {
+      const uint64_t len = c.varint(); const unsigned char* q = c.take(len);
+      if (field == 7) e.sliced = true;
+      if (field == 2) {   // TensorShapeProto: repeated Dim dim = 2 { int64 size = 1; string name = 2 }
+        ByteCursor s{q, q + len};
+        while (!s.done()) {
+          const uint64_t t2 = s.varint();
+          if ((t2 & 7) == 2) {
+            const uint64_t l2 = s.varint(); const unsigned char* d = s.take(l2);
+            if ((t2 >> 3) == 2) { ByteCursor dc{d, d + l2}; int64_t dim = 0; while (!dc.done()) { const uint64_t t3 = dc.varint(); if ((t3 & 7) == 0) { const uint64_t x = dc.varint(); if ((t3 >> 3) == 1) dim = (int64_t)x; } else if ((t3 & 7) == 2) dc.take(dc.varint()); else throw std::runtime_error("tensor bundle: bad TensorShapeProto.Dim"); } e.shape.push_back(dim); }
+          } else if ((t2 & 7) == 0) s.varint();
+          else throw std::runtime_error("tensor bundle: bad TensorShapeProto");
+        }
+      }
+    } else throw std::runtime_error("tensor bundle: unsupported protobuf wire type in BundleEntryProto");
+  }
+  return e;
+}
+
+// <prefix>.index -> every key's entry.  Table layout: data blocks, metaindex block, index block, 48-byte footer
+// (metaindex handle, index handle, padding, magic 0xdb4775248b80fb57 little-endian).
+inline Bundle read_bundle_index(const std::string& prefix) {
+  const std::vector<unsigned char> file = read_file((prefix + ".index").c_str());
+  if (file.size() < 48) throw std::runtime_error("tensor bundle index: file shorter than a table footer");
+  const unsigned char* foot = &file[file.size() - 48];
+  if (le32(foot + 40) != 0x8b80fb57u || le32(foot + 44) != 0xdb477524u) throw std::runtime_error("tensor bundle index: bad table magic (not a TensorFlow checkpoint index)");
+  ByteCursor fc{foot, foot + 40};
+  fc.varint(); fc.varint();   // metaindex handle
+  const uint64_t idx_off = fc.varint(), idx_size = fc.varint();
+  Bundle b; bool header_seen = false;
+  table_block(file, idx_off, idx_size, [&](const std::string&, const unsigned char* hv, size_t hn) {
+    ByteCursor hc{hv, hv + hn}; const uint64_t off = hc.varint(), size = hc.varint();
+    table_block(file, off, size, [&](const std::string& key, const unsigned char* v, size_t n) {
+      if (key.empty()) {   // BundleHeaderProto: num_shards = 1, endianness = 2 (0 little), version = 3
+        header_seen = true; ByteCursor c{v, v + n};
+        while (!c.done()) {
+          const uint64_t tag = c.varint();
+          if ((tag & 7) == 0) { const uint64_t x = c.varint(); if ((tag >> 3) == 1) b.num_shards = (int)x; if ((tag >> 3) == 2 && x != 0) throw std::runtime_error("tensor bundle: big-endian checkpoint"); }
+          else if ((tag & 7) == 2) c.take(c.varint());
+          else throw std::runtime_error("tensor bundle: bad BundleHeaderProto");
+        }
+      } else b.entries[key] = parse_bundle_entry(v, n);
+    });
+  });
+  if (!header_seen) throw std::runtime_error("tensor bundle index: no header entry");
+  return b;
+}
+
+// One DT_FLOAT tensor of the bundle, appended to out; the shape must be exactly `want`.
+inline void read_bundle_float(const std::string& prefix, const Bundle& b, const std::string& key, const std::vector<int64_t>& want,
+                              std::map<int, std::vector<unsigned char>>& shards, std::vector<float>& out) {
+  auto it = b.entries.find(key);
+  if (it == b.entries.end()) throw std::runtime_error("SavedModel has no variable '" + key + "'");
+  const BundleEntry& e = it->second;
+  if (e.dtype != 1) throw std::runtime_error("variable '" + key + "' is not DT_FLOAT (dtype " + std::to_string(e.dtype) + ")");
+  if (e.sliced) throw std::runtime_error("variable '" + key + "' is stored as slices");
+  if (e.shape != want) {
+    std::string got, exp; for (auto d : e.shape) got += std::to_string(d) + ","; for (auto d : want) exp += std::to_string(d) + ",";
+    throw std::runtime_error("variable '" + key + "' has shape [" + got + "] instead of [" + exp + "]");
+  }
+  int64_t count = 1; for (auto d : want) count *= d;
+  if (e.size != count * 4) throw std::runtime_error("variable '" + key + "': byte size does not match its shape");
+  if (e.shard < 0 || e.shard >= b.num_shards) throw std::runtime_error("variable '" + key + "': shard id out of range");
+  if (!shards.count(e.shard)) { char name[64]; std::snprintf(name, sizeof(name), ".data-%05d-of-%05d", e.shard, b.num_shards); shards[e.shard] = read_file((prefix + name).c_str()); }
+  const std::vector<unsigned char>& d = shards[e.shard];
+  if (e.offset < 0 || (uint64_t)e.offset + (uint64_t)e.size > d.size()) throw std::runtime_error("variable '" + key + "' lies outside its data shard");
+  if (e.has_crc && crc32c_mask(crc32c(&d[e.offset], (size_t)e.size)) != e.crc) throw std::runtime_error("variable '" + key + "': CRC32C mismatch");
+  const size_t at = out.size(); out.resize(at + (size_t)count);
+  std::memcpy(&out[at], &d[e.offset], (size_t)e.size);
+}
+
+// The actor of scripts/rover_training_1.py:26-35 out of <dir>/variables/variables.{index,data-*}: Keras names the i-th
+// layer that owns weights `layer_with_weights-i`, a Dense layer's variables `kernel` [in,out] and `bias` [out].
+inline std::vector<float> read_saved_model_actor(const std::string& dir, const int* dims, int n_layers) {
+  const std::string prefix = dir + "/variables/variables";
+  const Bundle b = read_bundle_index(prefix);
+  std::map<int, std::vector<unsigned char>> shards; std::vector<float> w;
+  for (int l = 0; l < n_layers; l++) {
+    const std::string base = "layer_with_weights-" + std::to_string(l) + "/";
+    read_bundle_float(prefix, b, base + "kernel/.ATTRIBUTES/VARIABLE_VALUE", {dims[l], dims[l + 1]}, shards, w);
+    read_bundle_float(prefix, b, base + "bias/.ATTRIBUTES/VARIABLE_VALUE", {dims[l + 1]}, shards, w);
+  }
+  if (b.entries.count("layer_with_weights-" + std::to_string(n_layers) + "/kernel/.ATTRIBUTES/VARIABLE_VALUE"))
+    throw std::runtime_error("SavedModel has more than " + std::to_string(n_layers) + " weight layers: not the actor of rover_training_1.py");
+  return w;
 }
 
 }  // namespace tfode_fmt

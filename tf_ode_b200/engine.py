@@ -25,6 +25,7 @@ EXPORTS = [
     "tfode_policy_infer",
     "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
     "tfode_heightmap_load_png", "tfode_heightmap_decode_png", "tfode_free",
+    "tfode_savedmodel_read_actor", "tfode_batch_load_policy_saved_model",
 ]
 
 
@@ -69,6 +70,8 @@ def load_library():
     L.tfode_batch_load_model_trees.argtypes = [vp, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t, i32, i32, i32]
     L.tfode_model_tree_infer.argtypes = [vp, vp, i32, vp, vp]
     L.tfode_batch_get_tree_nodes.argtypes = [vp, vp]
+    L.tfode_savedmodel_read_actor.argtypes = [C.c_char_p, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_size_t)]
+    L.tfode_batch_load_policy_saved_model.argtypes = [vp, C.c_char_p]
     L.tfode_heightmap_load_png.argtypes = [C.c_char_p, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.tfode_heightmap_decode_png.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.tfode_free.argtypes = [vp]
@@ -114,6 +117,19 @@ def load_heightmap_png(path_or_bytes, z_scale=0.3):
         return np.ctypeslib.as_array(h, shape=(nr.value, nc.value)).copy()
     finally:
         L.tfode_free(h)
+
+
+def read_saved_model_actor(saved_model_dir):
+    """TF_model's constructor (tf_cpp_binding.cc:14-66) without TensorFlow: the actor saved by
+    `td3.actor.save( session_dir + '/actor' )` (scripts/rover_training_1.py:90,121) -> float32 blob W1 b1 W2 b2 W3 b3."""
+    L = load_library()
+    w, n = C.POINTER(C.c_float)(), C.c_size_t(0)
+    if L.tfode_savedmodel_read_actor(os.fsencode(saved_model_dir), C.byref(w), C.byref(n)) != 0:
+        raise TfodeError(L.tfode_last_error(None).decode())
+    try:
+        return np.ctypeslib.as_array(w, shape=(n.value,)).copy()
+    finally:
+        L.tfode_free(w)
 
 
 def _hp(a):
@@ -183,6 +199,10 @@ class RoverBatch:
     def load_policy(self, w):
         w = np.ascontiguousarray(w, dtype=np.float32)
         self._ck(self.L.tfode_batch_load_policy(self.h, _hp(w), w.size))
+
+    def load_policy_saved_model(self, saved_model_dir):
+        """Rover_1_tf's `actor_path` (src/rover_1_tf.cc:24): the SavedModel directory itself."""
+        self._ck(self.L.tfode_batch_load_policy_saved_model(self.h, os.fsencode(saved_model_dir)))
 
     def load_model_trees(self, yaml_1, yaml_2, oblique=False, degree=1, interaction_only=False):
         """Rover_1_mt's constructor (src/rover_1_mt.cc:13-27): YAML text of tree 1 (steering rate) and tree 2 (boggie torque)."""

@@ -8,7 +8,9 @@
 //   a path prefix P such that P1.yaml and P2.yaml exist -> Rover_1_mt with those two model trees, exactly the
 //       reference's argv[3] (scene_1_mt.cc:25-30; default there "../scripts/tree_params2_");
 //   "random" (default here; BASELINE config 2) -> U(-15,15) deg/s and U(-25,25) N.m at every IC tick;
-//   any other path -> a raw fp32 actor blob (272 898 floats), which selects the Rover_1_tf MLP controller.
+//   a directory holding variables/variables.index -> the actor SavedModel of scripts/rover_training_1.py:90,121
+//       (Rover_1_tf's `actor_path`, src/rover_1_tf.cc:24), read without TensorFlow;
+//   any other path -> a raw fp32 actor blob (272 898 floats); both select the Rover_1_tf MLP controller.
 // `--scene file.png` builds the HeightField of scene_1_mt.cc:66 from that image (3 x 3 m at (1,0,-0.3)).
 // Environments are sharded over G GPUs by contiguous ranges, one host thread and one handle per GPU; there is no
 // data-path collective (environments are independent).  Prints the reference's result line for the first
@@ -61,7 +63,11 @@ int main(int argc, char* argv[]) {
   std::vector<float> weights;
   bool trees = false;
   if (policy != "random") { std::ifstream t1(policy + "1.yaml"), t2(policy + "2.yaml"); trees = (bool)t1 && (bool)t2; }
-  if (policy != "random" && !trees) {
+  if (policy != "random" && !trees && (bool)std::ifstream(policy + "/variables/variables.index")) {
+    float* w = nullptr; size_t n = 0;
+    if (tfode_savedmodel_read_actor(policy.c_str(), &w, &n) != TFODE_OK) throw std::runtime_error(tfode_last_error(nullptr));
+    weights.assign(w, w + n); tfode_free(w);
+  } else if (policy != "random" && !trees) {
     std::ifstream f(policy, std::ios::binary);
     if (!f) throw std::runtime_error("cannot open actor blob " + policy);
     f.seekg(0, std::ios::end); size_t bytes = (size_t)f.tellg(); f.seekg(0);

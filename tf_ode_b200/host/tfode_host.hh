@@ -298,9 +298,18 @@ class Rover_1 : public Robot {
   float* _d_act = nullptr; float* _d_speed = nullptr;
 };
 
-// src/rover_tf.hh / src/rover_1_tf.cc: the actor is a raw fp32 blob (W1 b1 W2 b2 W3 b3, Keras [in,out] layout) instead of a SavedModel directory.
+// src/rover_tf.hh / src/rover_1_tf.cc: the actor is either the reference's own `actor_path` (the SavedModel directory written by
+// td3.actor.save, read without TensorFlow by tfode_savedmodel_read_actor) or a raw fp32 blob (W1 b1 W2 b2 W3 b3, Keras [in,out] layout).
 class Rover_1_tf : public Rover_1 {
  public:
+  Rover_1_tf(ode::Environment& env, const Vector3d& pose, const char* actor_path, bool tensor_cores = true) : Rover_1(env, pose) {
+    float* w = nullptr; size_t n = 0;
+    if (tfode_savedmodel_read_actor(actor_path, &w, &n) != TFODE_OK) throw std::runtime_error(tfode_last_error(nullptr));
+    TfodeBatchConfig& c = env.config();
+    c.controller = TFODE_CTRL_MLP; c.fork_callback = 1; c.policy_precision = tensor_cores ? TFODE_POLICY_TC : TFODE_POLICY_FP32;
+    try { env._set_policy(w, n); } catch (...) { tfode_free(w); throw; }
+    tfode_free(w);
+  }
   Rover_1_tf(ode::Environment& env, const Vector3d& pose, const float* actor_weights, size_t n_floats, bool tensor_cores = true) : Rover_1(env, pose) {
     TfodeBatchConfig& c = env.config();
     c.controller = TFODE_CTRL_MLP; c.fork_callback = 1; c.policy_precision = tensor_cores ? TFODE_POLICY_TC : TFODE_POLICY_FP32;
