@@ -9,6 +9,10 @@ N=1 workload (default) = BASELINE.json configs[1]: rover_1_mt, 4096 rovers on th
 random actions every 0.5 s.  N>1: every rank owns 4096 more environments (weak scaling, no data-path collective).
 `--impl reference` times the CPU path instead: the oracle port (the reference itself cannot be built here: libode,
 Eigen, Boost are absent -- DESIGN.md), all host threads, on a bounded sample of the same workload.
+Every arm -- device-resident `value`, host-buffer `e2e`, the CPU arms -- starts from a reset and times the same episode
+segment (sub-steps W*100 .. (W+K)*100): a sub-step's cost drifts by +-20 % along the episode (19.3 ms per 100 sub-steps
+on the plane before the terrain, 28 ms with all wheels on the groove; tools/e2e_split.py), so arms timed on different
+segments are not comparable.
 """
 import argparse
 import json
@@ -23,6 +27,7 @@ sys.path.insert(0, ROOT)
 
 ALGO_BYTES_PER_ENV_STEP = 1680  # (read + write) x 840 B of persistent fp32 state
 SUBSTEPS = 100                  # env-steps per env per bench step (one launch)
+CPU_SAMPLE_ENVS = 4096          # the CPU arm steps at most this many environments of the workload
 
 WORKLOADS = {
     # name: (description, envs per GPU)
@@ -83,22 +88,39 @@ class ClockSampler:
         return out
 
 
-def run_reference(args, n_envs):
-    """The CPU arm: oracle<double> (reference-equivalent arithmetic), N envs over all host threads."""
+def cpu_segment(workload, n_envs, warmup, steps, max_env_steps=None):
+    """oracle<double> over all host threads on the GPU arm's own episode segment: from reset, `warmup` untimed then `steps` timed steps of
+    SUBSTEPS sub-steps (the cost of a sub-step drifts by +-20 % along the episode as the rovers reach the terrain, so the arms must cover
+    the same sub-steps).  Bounded sample: the first min(n_envs, CPU_SAMPLE_ENVS) environments, fewer if max_env_steps says so."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib
+    from tf_ode_b200 import abi, glorot_policy
     cores = os.cpu_count() or 1
-    sub = 20  # bounded sample per step: n_envs x 20 sub-steps
-    o = oracle_lib.Oracle(make_cfg(args.workload, n_envs), "double", threads=cores)
-    for _ in range(args.warmup):
-        o.step(sub)
+    n = min(n_envs, CPU_SAMPLE_ENVS)
+    if max_env_steps:
+        n = max(256, min(n, int(max_env_steps // ((warmup + steps) * SUBSTEPS)) // 256 * 256))
+    cfg = make_cfg(workload, n)
+    o = oracle_lib.Oracle(cfg, "double", threads=cores)
+    if cfg.controller == abi.CTRL_MLP:
+        o.load_policy(glorot_policy())
+    for _ in range(warmup):
+        o.step(SUBSTEPS)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        o.step(sub)
+    for _ in range(steps):
+        o.step(SUBSTEPS)
     dt = time.perf_counter() - t0
     o.close()
+    sample = ("%d envs x %d sub-steps per step, episode sub-steps %d..%d from reset (same scene/controller/segment as the GPU arm), oracle<double> "
+              "(reference-equivalent fp64 restatement; real libode unavailable on this box), %d std::threads"
+              % (n, SUBSTEPS, warmup * SUBSTEPS, (warmup + steps) * SUBSTEPS, cores))
+    return n, dt, cores, sample
+
+
+def run_reference(args, n_envs):
+    """The CPU arm: oracle<double> (reference-equivalent arithmetic), N envs over all host threads."""
+    n_envs, dt, cores, sample = cpu_segment(args.workload, n_envs, args.warmup, args.steps)
+    sub = SUBSTEPS
     v = n_envs * sub * args.steps / dt
-    sample = "%d envs x %d sub-steps per step (same scene/controller as the GPU arm), oracle<double>, %d std::threads" % (n_envs, sub, cores)
     return {
         "impl": "reference", "metric": "rover env-steps/sec", "value": v, "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -155,6 +177,7 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     # -------- device-resident arm: state already in HBM, one fused launch per step ------------------------------------------------
+    g.reset()
     for _ in range(args.warmup):
         g.step(SUBSTEPS)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
@@ -187,6 +210,7 @@ def main():
     done = torch.zeros(n_envs, dtype=torch.uint8).pin_memory().numpy()
     rng = np.random.RandomState(rank)
     external = cfg.controller == abi.CTRL_EXTERNAL
+    g.reset()  # same episode segment as the device-resident arm: sub-steps W*100 .. (W+K)*100 from reset
     for _ in range(args.warmup):
         g.rollout_host(act if external else None, SUBSTEPS, obs, rew, done)
     barrier()
@@ -203,18 +227,8 @@ def main():
     # -------- CPU baseline beside it (rank 0, N=1 only): bounded sample of the same workload ------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        sys.path.insert(0, os.path.join(ROOT, "tests"))
-        import oracle_lib
-        cores = os.cpu_count() or 1
-        cn, cs = min(n_envs, 4096), 400
-        o = oracle_lib.Oracle(make_cfg(args.workload, cn), "double", threads=cores)
-        if cfg.controller == abi.CTRL_MLP:
-            o.load_policy(glorot_policy())
-        o.step(50)
-        t0 = time.perf_counter(); o.step(cs); dtc = time.perf_counter() - t0
-        o.close()
-        cpu = {"value": cn * cs / dtc, "unit": "env-steps/s", "cores": cores, "kind": "port",
-               "sample": "%d envs x %d steps of the same scene/controller, oracle<double> (reference-equivalent fp64 restatement; real libode unavailable on this box), %d std::threads" % (cn, cs, cores)}
+        cn, dtc, cores, sample = cpu_segment(args.workload, n_envs, args.warmup, args.steps, max_env_steps=12e6)
+        cpu = {"value": cn * SUBSTEPS * args.steps / dtc, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample}
 
     if rank == 0:
         peaks = {}
@@ -237,7 +251,8 @@ def main():
             "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][0], "envs_per_gpu": n_envs, "substeps_per_step": SUBSTEPS,
                        "pgs_iters": cfg.pgs_iters, "dt": 0.001, "sharding": "contiguous env ranges, no data-path collective",
-                       "l2": "256 MiB fill between timed steps, outside the per-step CUDA-event pairs"},
+                       "l2": "256 MiB fill between timed steps, outside the per-step CUDA-event pairs",
+                       "segment": "every arm (value, e2e, CPU) starts from reset and times episode sub-steps %d..%d" % (args.warmup * SUBSTEPS, (args.warmup + args.steps) * SUBSTEPS)},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_unit": "bytes per launch (ncu dram read+write)", "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
                          "kernel": "tfode::step_kernel", "kernel_ms": kern_ms,
