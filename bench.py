@@ -88,6 +88,13 @@ class ClockSampler:
         return out
 
 
+def action_tape(rank, k, n_envs):
+    """Step k's externally supplied actions of rank `rank`: U(-15,15) deg/s, U(-25,25) N.m per environment.  Every arm feeds the same tape
+    (they act until a scene's own controller takes over at its first IC tick), so every arm simulates the same trajectories."""
+    import numpy as np
+    return (np.random.RandomState(100003 * rank + k).uniform(-1, 1, size=(n_envs, 2)) * np.array([15.0, 25.0])).astype(np.float32)
+
+
 def cpu_segment(workload, n_envs, warmup, steps, max_env_steps=None):
     """oracle<double> over all host threads on the GPU arm's own episode segment: from reset, `warmup` untimed then `steps` timed steps of
     SUBSTEPS sub-steps (the cost of a sub-step drifts by +-20 % along the episode as the rovers reach the terrain, so the arms must cover
@@ -103,11 +110,12 @@ def cpu_segment(workload, n_envs, warmup, steps, max_env_steps=None):
     o = oracle_lib.Oracle(cfg, "double", threads=cores)
     if cfg.controller == abi.CTRL_MLP:
         o.load_policy(glorot_policy())
-    for _ in range(warmup):
-        o.step(SUBSTEPS)
+    tape = [action_tape(0, k, n_envs)[:n] for k in range(warmup + steps)]
+    for k in range(warmup):
+        o.set_actions(tape[k]); o.step(SUBSTEPS)
     t0 = time.perf_counter()
-    for _ in range(steps):
-        o.step(SUBSTEPS)
+    for k in range(warmup, warmup + steps):
+        o.set_actions(tape[k]); o.step(SUBSTEPS)
     dt = time.perf_counter() - t0
     o.close()
     sample = ("%d envs x %d sub-steps per step, episode sub-steps %d..%d from reset (same scene/controller/segment as the GPU arm), oracle<double> "
@@ -177,17 +185,20 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
 
     # -------- device-resident arm: state already in HBM, one fused launch per step ------------------------------------------------
+    tape = [action_tape(rank, k, n_envs) for k in range(args.warmup + args.steps)]   # the same inputs for every arm
+    tape_dev = [torch.from_numpy(t).cuda() for t in tape]
     g.reset()
-    for _ in range(args.warmup):
-        g.step(SUBSTEPS)
+    for k in range(args.warmup):
+        g.set_actions(tape_dev[k]); g.step(SUBSTEPS)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
     clocks = ClockSampler(local)
     l0 = g.launch_count
     t_wall = time.perf_counter()
-    for a, b in ev:
+    for k, (a, b) in enumerate(ev):
         flush.fill_(1)  # L2 flush between timed iterations, outside the event pair
         a.record()
+        g.set_actions(tape_dev[args.warmup + k])  # device-resident inputs: set_actions_kernel, counted in gpu_launches
         g.step(SUBSTEPS)
         b.record()
     barrier()
@@ -201,22 +212,21 @@ def main():
     tot_ms = float(tot_ms.item())
     units = n_envs * SUBSTEPS * args.steps * world
     value = units / (tot_ms * 1e-3)
-    step_launches = launches / args.steps  # step kernel (+ policy kernels for the MLP workload)
+    step_launches = launches / args.steps  # set_actions_kernel + step kernel (+ policy kernels for the MLP workload)
 
     # -------- end-to-end arm: HOST buffers through the C-ABI round trip (H2D actions, step, D2H obs/reward/done) --------------------
     act = torch.zeros(n_envs, 2, dtype=torch.float32).pin_memory().numpy()
     obs = torch.zeros(n_envs, 17, dtype=torch.float32).pin_memory().numpy()
     rew = torch.zeros(n_envs, dtype=torch.float32).pin_memory().numpy()
     done = torch.zeros(n_envs, dtype=torch.uint8).pin_memory().numpy()
-    rng = np.random.RandomState(rank)
-    external = cfg.controller == abi.CTRL_EXTERNAL
-    g.reset()  # same episode segment as the device-resident arm: sub-steps W*100 .. (W+K)*100 from reset
-    for _ in range(args.warmup):
-        g.rollout_host(act if external else None, SUBSTEPS, obs, rew, done)
+    g.reset()  # same episode segment and inputs as the device-resident arm: sub-steps W*100 .. (W+K)*100 from reset
+    for k in range(args.warmup):
+        act[:] = tape[k]
+        g.rollout_host(act, SUBSTEPS, obs, rew, done)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        act[:] = rng.uniform(-1, 1, size=act.shape) * np.array([15.0, 25.0], np.float32)
+    for k in range(args.steps):
+        act[:] = tape[args.warmup + k]  # this step's inputs reach the pinned buffer inside the timed region
         g.rollout_host(act, SUBSTEPS, obs, rew, done)  # actions are uploaded every step; scenes with their own controller overwrite them at IC ticks
     barrier()
     e2e_t = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
