@@ -66,6 +66,14 @@ class ClockSampler:
         except OSError:
             self.p = None
 
+    def mark(self):
+        """Start of the timed region: samples written before this point (the warm-up steps, same load) are used only if nvidia-smi
+        delivers none after it (a 0.2 s timed region on an 8-GPU box can end before its first 100 ms tick is written)."""
+        try:
+            self.skip = sum(1 for _ in open(self.f.name))
+        except OSError:
+            self.skip = 0
+
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
         if self.p is None:
@@ -78,6 +86,11 @@ class ClockSampler:
         self.f.flush(); self.f.seek(0)
         rows = [r.split(",") for r in self.f.read().strip().splitlines() if r.count(",") >= 6]
         os.unlink(self.f.name)
+        skip = getattr(self, "skip", 0)
+        if len(rows) > skip:
+            rows = rows[skip:]
+        elif rows:
+            out["note"] = "sampled during the warm-up steps (same load); the timed region ended before nvidia-smi's next tick"
         if not rows:
             return out
         sm = sorted(float(r[0]) for r in rows)
@@ -188,11 +201,12 @@ def main():
     tape = [action_tape(rank, k, n_envs) for k in range(args.warmup + args.steps)]   # the same inputs for every arm
     tape_dev = [torch.from_numpy(t).cuda() for t in tape]
     g.reset()
+    clocks = ClockSampler(local)  # started before the warm-up so that nvidia-smi is up when the timed region begins
     for k in range(args.warmup):
         g.set_actions(tape_dev[k]); g.step(SUBSTEPS)
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
-    clocks = ClockSampler(local)
+    clocks.mark()
     l0 = g.launch_count
     t_wall = time.perf_counter()
     for k, (a, b) in enumerate(ev):
