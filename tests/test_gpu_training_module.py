@@ -60,3 +60,19 @@ def test_eval_prints_the_reference_result_line():
         assert t == pytest.approx(float(np.float32(s.time_steps) * np.float32(0.001)))
         assert rmoy == pytest.approx(s.total_reward / t, rel=1e-12)
         assert ok == (abs(x) >= 0.6)
+
+
+def test_trial_takes_the_reference_argument_a_saved_model_directory(tmp_path):
+    """trial( session_dir + '/actor' ) (scripts/rover_training_1.py:121): the directory gives the same experience as its weight blob."""
+    from test_formats import write_bundle
+    w = glorot_policy()
+    t, o = {}, 0
+    for l, (i, j) in enumerate(((17, 512), (512, 512), (512, 2))):
+        t["layer_with_weights-%d/kernel/.ATTRIBUTES/VARIABLE_VALUE" % l] = (w[o:o + i * j].reshape(i, j).copy(), 1); o += i * j
+        t["layer_with_weights-%d/bias/.ATTRIBUTES/VARIABLE_VALUE" % l] = (w[o:o + j].copy(), 1); o += j
+    write_bundle(str(tmp_path / "actor" / "variables" / "variables"), t)
+    a = training_module.trial(str(tmp_path / "actor"), n_episodes=1, **FAST)
+    b = training_module.trial(w, n_episodes=1, **FAST)
+    assert len(a) == len(b) > 0
+    for ra, rb in zip(a, b):
+        assert ra[0] == rb[0] and ra[1] == rb[1] and ra[2] == rb[2] and ra[3] == rb[3] and ra[4] == rb[4]

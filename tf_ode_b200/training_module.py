@@ -5,19 +5,29 @@ Reference:  trial(path_to_model_dir) -> list of (state[17], (steering_rate, bogg
             for ONE episode of ONE rover driven by the SavedModel actor at that path with e-greedy exploration
             (simulation("trial", ...), src/rover_training_1.cc:41-224); eval(path) runs one episode without exploration
             and prints the result line (:203-209).
-Here:       the actor is the fp32 weight blob the engine takes (tfode_batch_load_policy; no TensorFlow on this box),
-            and one call runs `n_episodes` independent episodes in one batch on the GPU.  trial() returns one such list
+Here:       the actor is either that same SavedModel directory (a str / os.PathLike: its checkpoint variables are read by
+            tfode_savedmodel_read_actor, no TensorFlow involved) or the fp32 weight blob the engine takes
+            (tfode_batch_load_policy), and one call runs `n_episodes` independent episodes in one batch on the GPU.  trial() returns one such list
             per episode, built from the engine's transition ring; the terminal patch and the end-of-episode penalties
             (-2 beyond y_max, -5 upside-down, :212-224) are applied on the device.
 There is no CPU path: this calls the C-ABI library and needs a B200.
 """
+import os
+
 import numpy as np
 
 from . import abi
 from .config import make_config
-from .engine import RoverBatch
+from .engine import RoverBatch, read_saved_model_actor
 
 TIMEOUT_STEPS = 60000  # float timeout(60) at 1 ms steps (src/rover_training_1.cc:119)
+
+
+def _actor(actor):
+    """path_to_model_dir (the reference's argument) or a weight blob -> float32 blob."""
+    if isinstance(actor, (str, bytes, os.PathLike)):
+        return read_saved_model_actor(actor)
+    return np.asarray(actor, np.float32)
 
 
 def _run_episodes(actor_weights, n_episodes, exploration, seed, device, policy_precision, cfg_overrides):
@@ -60,7 +70,7 @@ def rows_to_experience(rows, n_episodes):
 def trial(actor_weights, n_episodes=1, seed=20260411, device=0, policy_precision=abi.POLICY_FP32, **cfg_overrides):
     """`n_episodes` x simulation("trial", actor): exploration on, randomised step yaw and IC start.  Returns a list of
     `n_episodes` experience lists; with n_episodes == 1 the single list itself, like the reference's trial()."""
-    rows, _, _ = _run_episodes(np.asarray(actor_weights, np.float32), n_episodes, True, seed, device, policy_precision, cfg_overrides)
+    rows, _, _ = _run_episodes(_actor(actor_weights), n_episodes, True, seed, device, policy_precision, cfg_overrides)
     exp = rows_to_experience(rows, n_episodes)
     return exp[0] if n_episodes == 1 else exp
 
@@ -76,7 +86,7 @@ def result_line(ok, t, x, y, rmoy, colour=True):
 def eval(actor_weights, n_episodes=1, seed=20260411, device=0, policy_precision=abi.POLICY_FP32, colour=True, file=None, **cfg_overrides):  # noqa: A001 (the reference's name)
     """`n_episodes` x simulation("eval", actor): no exploration; prints one result line per episode and returns
     (success, t, x, y, Rmoy) tuples."""
-    _, states, cfg = _run_episodes(np.asarray(actor_weights, np.float32), n_episodes, False, seed, device, policy_precision, cfg_overrides)
+    _, states, cfg = _run_episodes(_actor(actor_weights), n_episodes, False, seed, device, policy_precision, cfg_overrides)
     getpos = np.array([-0.1095, -0.023, 0.0075])  # Rover_1::GetPosition's point of the main body (src/rover_1.cc:248-253)
     res = []
     for s in states:
