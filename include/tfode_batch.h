@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define TFODE_ABI_VERSION 1
+#define TFODE_ABI_VERSION 2
 
 /* ---- model sizes (src/rover_1.cc:116-217; src/rover_training_1.cc:90-98) -- */
 #define TFODE_NBODY_ROVER 10 /* main, battery, rear, boggie, front fork, rear fork, wheel0..3 */
@@ -29,6 +29,7 @@ extern "C" {
 #define TFODE_NACT 2         /* steering rate [deg/s], boggie torque [N.m] */
 #define TFODE_MLP_HIDDEN 512 /* scripts/rover_training_1.py:26-35 */
 #define TFODE_TRANSITION_WIDTH 40 /* env_id, s[17], a[2], r, terminal, s'[17], pad */
+#define TFODE_ROLLOUT_WIDTH 24    /* obs17, reward, done, last episode return / steps, episodes done, global env id, pad */
 #define TFODE_TREE_INPUTS 14       /* Rover_1_mt::GetState(flip=false, full=false), src/rover_1_mt.cc:30-52 */
 #define TFODE_TREE_MAX_FEATURES 119 /* 14 + 14*15/2: Polynomial_model_tree of degree 2 (model_tree.cc:91-123) */
 
@@ -59,8 +60,11 @@ enum {
 
 /* ---- policy arithmetic ----------------------------------------------------- */
 enum {
-  TFODE_POLICY_FP32 = 0, /* CUDA-core fp32 FMA (bit-comparable with the oracle within 1e-5) */
-  TFODE_POLICY_TC = 1    /* tcgen05 tensor-core path (bf16 operands, fp32 TMEM accumulators) */
+  TFODE_POLICY_FP32 = 0, /* fp32, one fma per weight in input order (bit-identical to the oracle): inside tfode_batch_step the
+                            actor runs fused in step_kernel at each environment's own IC tick and writes the servo / boggie
+                            setpoints directly; tfode_policy_infer uses the batched CUDA-core kernel */
+  TFODE_POLICY_TC = 1    /* tcgen05 tensor-core path (bf16 operands, fp32 TMEM accumulators): environments park at their IC
+                            tick and a batched GEMM kernel serves the parked list between step_kernel launches */
 };
 
 /* ---- termination reasons (src/rover_training_1.cc:142) -------------------- */
@@ -225,12 +229,30 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps);
  * obs17 [n,17] float (unscaled), reward [n] (last IC-tick reward), done [n] (episode ended
  * during the last tfode_batch_step call), contact_count [n] (last world step). */
 int tfode_batch_observe(TfodeBatch* b, float* obs17, float* reward, uint8_t* done, int32_t* contact_count);
+/* What one policy tick hands the trainer, one packed row per env so that a single collective (or copy) moves it
+ * (the experience list / result line of src/rover_training_1.cc:203-224,243-246): DEVICE float [n, TFODE_ROLLOUT_WIDTH] =
+ * obs17 | reward of the last IC tick | done during the last call | return, steps of the last finished episode |
+ * episodes finished | global env id | 0. */
+int tfode_batch_pack_rollout(TfodeBatch* b, float* rows_dev);
 /* pos(3) quat(4) linvel(3) angvel(3) of the 12 bodies: DEVICE float [n,12,13]. */
 int tfode_batch_get_bodies(TfodeBatch* b, float* out_dev);
 
-/* Experience tuples (src/rover_1_tf.cc:120-122, rover_training_1.cc:212-224) appended since the
- * last drain: DEVICE float [max_rows, TFODE_TRANSITION_WIDTH]; *n_rows_host receives the count. */
-int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, int* n_rows_host);
+/* Experience tuples (src/rover_1_tf.cc:120-122, rover_training_1.cc:212-224) appended since the last drain, in
+ * completion order: DEVICE float [max_rows, TFODE_TRANSITION_WIDTH].
+ *   *n_rows_host    rows written to out_dev (HOST int);
+ *   *n_dropped_host rows produced beyond the ring's transition_capacity since the last drain and therefore lost
+ *                   (HOST int, may be NULL; 0 means the experience list is complete -- size transition_capacity for
+ *                   episodes_per_call x ticks_per_episode rows, the default 4*n_envs covers 2 s of simulated time per call).
+ * If the pending rows do not fit max_rows (or out_dev is NULL) NOTHING is consumed: the call returns TFODE_EINVAL with
+ * *n_rows_host = rows pending, so the caller can retry with a buffer of that many rows. */
+int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, int* n_rows_host, int* n_dropped_host);
+
+/* Contact-capacity audit.  The reference creates every contact dCollide returns (ode/environment.cc:101-128: up to 10 per
+ * geom pair, no per-world limit); this engine keeps max_contacts (<= 24) per environment and drops the excess in generation
+ * order.  *over_capacity_steps = environment sub-steps since creation (or the last reset of the counters) in which more
+ * contacts were generated than kept; *max_generated = the largest number one environment generated in one sub-step.
+ * A non-zero first value means trajectories deviate from the reference's for that reason.  HOST pointers, either may be NULL. */
+int tfode_batch_contact_stats(TfodeBatch* b, int64_t* over_capacity_steps, int64_t* max_generated, int reset);
 
 /* Host-buffer round trip used by the end-to-end measurement: H2D actions (may be NULL),
  * n_substeps, D2H obs17/reward/done (HOST pointers, pinned or pageable; any may be NULL). */

@@ -28,6 +28,7 @@ struct BatchBase {
   virtual void reset(const int32_t* ids, int n) = 0;
   virtual int last_rows(int env) = 0;
   virtual int max_pair_contacts() = 0;
+  virtual void contact_hist(uint64_t* out129) = 0;
   SharedScene scene;
   int n_threads = 1;
 };
@@ -79,6 +80,7 @@ template <class T> struct Batch : BatchBase {
     for (int i = 0; i < n; i++) envs[ids[i]].reset(envs[ids[i]].episode + 1);
   }
   int last_rows(int env) override { return envs[env].w.last_rows; }
+  void contact_hist(uint64_t* out) override { for (int i = 0; i < 129; i++) out[i] = 0; for (auto& e : envs) for (int i = 0; i < 129; i++) out[i] += e.contact_hist[i]; }
   int max_pair_contacts() override { int m = 0; for (auto& e : envs) m = std::max(m, e.max_pair_contacts); return m; }
 };
 
@@ -127,6 +129,7 @@ int orc_drain_transitions(void* h, float* out, int max_rows) { return static_cas
 void orc_reset(void* h, const int32_t* ids, int n) { static_cast<BatchBase*>(h)->reset(ids, n); }
 int orc_last_rows(void* h, int env) { return static_cast<BatchBase*>(h)->last_rows(env); }
 int orc_max_pair_contacts(void* h) { return static_cast<BatchBase*>(h)->max_pair_contacts(); }
+void orc_contact_hist(void* h, uint64_t* out129) { static_cast<BatchBase*>(h)->contact_hist(out129); }
 int orc_sizeof_state() { return (int)sizeof(TfodeEnvState); }
 int orc_sizeof_config() { return (int)sizeof(TfodeBatchConfig); }
 

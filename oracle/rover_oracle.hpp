@@ -196,6 +196,7 @@ template <class T> struct RoverSim {
   bool done = false, frozen = false; int term_reason = 0, n_contacts = 0, episodes_done = 0;
   double last_ep_return = 0, last_ep_x = 0, last_ep_y = 0; int64_t last_ep_steps = 0;
   int max_pair_contacts = 0;
+  uint32_t contact_hist[129] = {0};   // steps by number of generated contacts (before the engine's capacity), last bin = 128+
 
   // -------------------------------------------------------------- construction
   void init(const SharedScene* scene, uint32_t env_global_id) {
@@ -489,6 +490,7 @@ template <class T> struct RoverSim {
       }
     }
     n_contacts = total;
+    contact_hist[total < 128 ? total : 128]++;
   }
 
   // cylinder vs box/heightfield (D-CYLBOX, D-HF): 8 rim points per cap, the deepest penetrating

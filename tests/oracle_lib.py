@@ -38,6 +38,7 @@ def lib():
         L.orc_reset.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         L.orc_last_rows.argtypes = [C.c_void_p, C.c_int]
         L.orc_max_pair_contacts.argtypes = [C.c_void_p]
+        L.orc_contact_hist.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_rand_ints.argtypes = [C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_plane_space.argtypes = [C.c_void_p] * 3
         L.orc_philox.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]
@@ -144,6 +145,12 @@ class Oracle:
         else:
             ids = np.ascontiguousarray(ids, dtype=np.int32)
             self.L.orc_reset(self.h, _p(ids), ids.size)
+
+    def contact_hist(self):
+        """steps by number of GENERATED contacts (before the capacity cut), summed over environments; bin 128 = 128 or more."""
+        h = np.zeros(129, np.uint64)
+        self.L.orc_contact_hist(self.h, _p(h))
+        return h
 
     def last_rows(self, env=0):
         return self.L.orc_last_rows(self.h, env)

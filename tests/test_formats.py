@@ -136,7 +136,7 @@ def test_reference_heightmaps_match_the_committed_levels():
 
 
 def test_committed_heightmap_levels_have_the_reference_statistics():
-    lv = dict(np.load(os.path.join(GOLD, "heightmap_levels.npz")))
+    lv = dict(np.load(os.path.join(os.path.dirname(GOLD), os.pardir, "tf_ode_b200", "data", "heightmap_levels.npz")))
     assert lv["rock_step"].shape == (200, 200) and lv["rock_step"].min() == 0 and lv["rock_step"].max() == 254
     assert lv["rock_groove"].shape == (200, 200) and lv["rock_groove"].min() == 86 and lv["rock_groove"].max() == 255
     assert lv["rock_groove_large"].shape == (400, 400) and (lv["rock_groove_large"][0] == 255).all()

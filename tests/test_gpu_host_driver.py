@@ -62,7 +62,7 @@ def test_driver_with_the_reference_tree_file_prefix_matches_the_python_mirror():
 
 def test_driver_on_a_png_heightmap_scene_matches_the_python_mirror(tmp_path):
     """--scene file.png: the HeightField image constructor of the facade (ode/heightfield.hh:42-59) end to end."""
-    lv = np.load(os.path.join(ROOT, "tests", "golden", "heightmap_levels.npz"))["rock_groove"]
+    lv = np.load(os.path.join(ROOT, "tf_ode_b200", "data", "heightmap_levels.npz"))["rock_groove"]
     rgba = np.repeat(lv[..., None], 4, axis=2).astype(np.uint8); rgba[..., 3] = 255
     png = tmp_path / "heightmap_rock_groove.png"
     png.write_bytes(encode_png([rgba[y].tobytes() for y in range(lv.shape[0])], lv.shape[1], 8, 6, [0, 1, 2, 3, 4], idat_split=2))

@@ -114,21 +114,7 @@ def test_first_steps_against_double_oracle_are_tight():
         g.close(); o.close()
 
 
-def test_long_horizon_statistics_against_double_oracle():
-    """Episode-level statistics (north_star: 'episode-return statistics over long ones'): 256 envs x 4000 steps of
-    random actions on the step scene; means must agree within 3 standard errors of the difference."""
-    n, steps = 256, 4000
-    g, o = make_pair("steps_random", n, "double", auto_reset=0)
-    g.step(steps)
-    oo = oracle_lib.Oracle(SCENES["steps_random"](n, auto_reset=0), "double", threads=16)
-    oo.step(steps)
-    xg = np.array([oracle_lib.state_bodies(g.get_state(e))[0, 0:3] for e in range(n)])
-    xo = np.array([oo.bodies(e)[0, 0:3] for e in range(n)])
-    for k in range(2):
-        se = np.sqrt(xg[:, k].var() / n + xo[:, k].var() / n) + 1e-6
-        assert abs(xg[:, k].mean() - xo[:, k].mean()) <= 3 * se, (k, xg[:, k].mean(), xo[:, k].mean(), se)
-    assert abs(xg[:, 2].mean() - xo[:, 2].mean()) < 2e-3
-    g.close(); o.close(); oo.close()
+# (the long-horizon statistics contract -- >= 4096 complete episodes against oracle<double> -- lives in tests/test_gpu_configs.py)
 
 
 # ----------------------------------------------------------------------------------------------------------------------
@@ -269,7 +255,10 @@ def test_transitions_match_oracle_rows():
     g, o = make_pair("training_fast", n, transition_capacity=8 * n * 10)
     g.step(5000); o.step(5000)
     buf = torch.zeros(8 * n * 10, abi.TRANSITION_WIDTH, device="cuda")
+    with pytest.raises(Exception, match="rows pending"):
+        g.drain_transitions(buf, 3)               # too small: nothing is consumed, the error names the pending count
     cnt = g.drain_transitions(buf, buf.shape[0])
+    assert g.last_dropped == 0 and g.drain_transitions(buf, buf.shape[0]) == 0
     rows_o = o.drain_transitions()
     assert cnt == rows_o.shape[0] and cnt > n
     rows_g = buf[:cnt].cpu().numpy()
@@ -319,7 +308,9 @@ def test_config2_4096_envs_determinism_sharding_and_invariants():
     assert np.abs(np.linalg.norm(x[:, :, 3:7], axis=2) - 1).max() < 1e-5  # unit quaternions
     assert len(np.unique(x[:, 0, 1])) > n // 2  # random actions: envs diverged
     nc = torch.zeros(n, dtype=torch.int32, device="cuda"); a.observe(ncontacts=nc)
-    assert int(nc.min()) >= 0 and int(nc.max()) <= 64
+    assert int(nc.min()) >= 0 and int(nc.max()) <= a.cfg.max_contacts
+    over, mx = a.contact_stats()
+    assert over == 0 and mx <= a.cfg.max_contacts   # no contact was dropped anywhere in the 4096 x 1500 env-steps
     # spot-check 8 envs of the full batch against the oracle (bit-exact)
     o = oracle_lib.Oracle(mk(n, 0), "float", threads=16); o.step(steps)
     for e in (0, 1, 777, 1024, 2047, 3000, 4000, 4095):

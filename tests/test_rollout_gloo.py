@@ -50,12 +50,22 @@ class StubBatch:
     def load_policy(self, w):
         self.policy = np.array(w, copy=True)
 
-    def rollout_host(self, actions, n_substeps, obs, reward, done):
+    def step(self, n_substeps):
         self.t += n_substeps
+
+    def pack_rollout(self, rows):
         gid = np.arange(self.first, self.first + self.n)
-        obs[:] = gid[:, None] * 100 + np.arange(abi.NOBS)[None, :]
-        reward[:] = gid * 0.5 + self.t
-        done[:] = (gid % 3 == 0)
+        out = np.zeros((self.n, abi.ROLLOUT_WIDTH), np.float32)
+        out[:, : abi.NOBS] = gid[:, None] * 100 + np.arange(abi.NOBS)[None, :]
+        out[:, abi.NOBS] = gid * 0.5 + self.t
+        out[:, abi.NOBS + 1] = (gid % 3 == 0)
+        out[:, 22] = gid
+        rows.copy_(torch.from_numpy(out))
+
+    def drain_transitions(self, buf, max_rows):
+        n = 1 + self.first % 3   # ragged: ranks hold different numbers of experience rows
+        buf[:n, 0] = torch.arange(n, dtype=torch.float32) + 1000 * self.first
+        return n
 
     def close(self):
         pass
@@ -80,6 +90,23 @@ def _worker(rank, world, port, n_total, q):
             assert np.array_equal(done, gid % 3 == 0)
         else:
             assert out is None
+        # pipelined ticks: two gathers in flight (double-buffered rows), waited for out of order
+        h1 = r.tick_async(50); h2 = r.tick_async(50)
+        f2, f1 = h2.wait(), h1.wait()
+        if rank == 0:
+            gid = np.arange(n_total)
+            assert np.array_equal(f1[:, abi.NOBS].numpy(), (gid * 0.5 + 150).astype(np.float32))
+            assert np.array_equal(f2[:, abi.NOBS].numpy(), (gid * 0.5 + 200).astype(np.float32))
+            assert np.array_equal(f2[:, 22].numpy(), gid.astype(np.float32))   # global order, every environment once
+        else:
+            assert f1 is None and f2 is None
+        ex = r.gather_experience(8)
+        if rank == 0:
+            firsts = [rollout.shard_range(n_total, k, world)[0] for k in range(world)]
+            want = np.concatenate([np.arange(1 + f % 3) + 1000 * f for f in firsts]).astype(np.float32)
+            assert np.array_equal(ex[:, 0].numpy(), want)
+        else:
+            assert ex is None
         st = rollout.reduce_episode_stats(rank + 1, 2.0 * (rank + 1), 4.0 * (rank + 1), rank)
         assert st["episodes"] == 3 and abs(st["mean_return"] - 2.0) < 1e-12 and st["std_return"] < 1e-6
         q.put((rank, "ok"))

@@ -5,13 +5,14 @@ against the compiled library.
 """
 import ctypes as C
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 NBODY_ROVER = 10
 NBODY = 12
 NOBS = 17
 NACT = 2
 MLP_HIDDEN = 512
 TRANSITION_WIDTH = 40
+ROLLOUT_WIDTH = 24
 POLICY_NFLOATS = 17 * 512 + 512 + 512 * 512 + 512 + 512 * 2 + 2  # 272 898, scripts/rover_training_1.py:26-35
 
 SCENE_PLANE, SCENE_STEP_BOXES, SCENE_HEIGHTFIELD = 0, 1, 2

@@ -116,12 +116,12 @@ _LEVELS = None
 
 def reference_heightmap(kind):
     """The reference's own terrain: red-channel levels of env_data/heightmap_<kind>.png (committed as
-    tests/golden/heightmap_levels.npz by tools/make_golden.py, since /root/reference does not travel) turned into
+    tf_ode_b200/data/heightmap_levels.npz -- package data, written by tools/make_golden.py, since /root/reference does not travel) turned into
     heights exactly as ode/heightfield.hh:54 does (level * 0.3 / 255 in double), float32 [nrow, ncol], row 0 = top row.
     kind: 'rock_step' | 'rock_groove' | 'rock_groove_large'."""
     global _LEVELS
     if _LEVELS is None:
-        path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "heightmap_levels.npz")
+        path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data", "heightmap_levels.npz")
         _LEVELS = dict(np.load(path))
     return (_LEVELS[kind].astype(np.float64) * 0.3 / 255).astype(np.float32)
 

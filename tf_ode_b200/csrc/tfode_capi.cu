@@ -28,6 +28,7 @@ struct TfodeBatch {
   float* hf_h = nullptr; float* hf_bmax = nullptr;
   float* policy_in = nullptr; int* parked_list = nullptr; int* n_parked = nullptr;
   float* trans = nullptr; int* n_trans = nullptr; int trans_cap = 0;
+  unsigned long long* cstats = nullptr;   // contact-capacity audit counters (StepParams::cstats)
   float* ext_speed = nullptr;
   float4* ring4 = nullptr; Model* model_g = nullptr;    // Model::ring as float4 in global memory
   float* weights = nullptr;   // fp32 W1 b1 W2 b2 W3 b3
@@ -43,6 +44,19 @@ struct TfodeBatch {
   int* d_ids = nullptr; int ids_cap = 0;
   size_t smem_bytes = 0, smem_step = 0;
 };
+
+// Every entry point that takes a handle runs on the handle's own device, whatever device the calling thread had current
+// (a thread may own handles on several GPUs, or another library may have switched devices); the caller's device is restored.
+struct DeviceGuard {
+  int prev = -1; bool ok = true;
+  explicit DeviceGuard(const TfodeBatch* b) {
+    if (!b) return;
+    if (cudaGetDevice(&prev) != cudaSuccess) { prev = -1; ok = false; return; }
+    if (prev != b->cfg.device) { if (cudaSetDevice(b->cfg.device) != cudaSuccess) ok = false; } else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define GUARD(b) DeviceGuard guard_((b)); if ((b) && !guard_.ok) { (b)->err = "cudaSetDevice failed for this handle's device"; return TFODE_ECUDA; }
 
 #define CK(call)                                                                            \
   do {                                                                                      \
@@ -294,6 +308,8 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   CKC(cudaMalloc(&b->n_parked, sizeof(int) * 4));
   CKC(cudaMemset(b->n_parked, 0, sizeof(int) * 4));
   b->n_trans = b->n_parked + 1;
+  CKC(cudaMalloc(&b->cstats, sizeof(unsigned long long) * 2));
+  CKC(cudaMemset(b->cstats, 0, sizeof(unsigned long long) * 2));
   b->trans_cap = cfg->transition_capacity > 0 ? cfg->transition_capacity : 4 * n;
   CKC(cudaMalloc(&b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)b->trans_cap));
   CKC(cudaMalloc(&b->ext_speed, sizeof(float) * (size_t)n));
@@ -307,7 +323,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   std::memset(&P, 0, sizeof(P));
   P.rec = b->rec; P.budget = b->budget; P.n_envs = n; P.set_budget = -1; P.cfg = *cfg; P.cfg.hf_heights = nullptr;
   P.policy_in = b->policy_in; P.parked_list = b->parked_list; P.n_parked = b->n_parked;
-  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.ext_speed = nullptr; P.ring4 = b->ring4; P.model = b->model_g;
+  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.cstats = b->cstats; P.policy_w = nullptr; P.ext_speed = nullptr; P.ring4 = b->ring4; P.model = b->model_g;
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD) {
     const int nc = cfg->hf_ncol, nr = cfg->hf_nrow;
     const int nbx = (nc + 7) / 8, nbz = (nr + 7) / 8;
@@ -344,9 +360,10 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
 
 void tfode_batch_destroy(TfodeBatch* b) {
   if (!b) return;
+  DeviceGuard guard_(b);
   for (int t = 0; t < 2; t++) { cudaFree(b->tree_nodes[t]); cudaFree(b->tree_params[t]); }
   cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
-  cudaFree(b->n_parked); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
+  cudaFree(b->n_parked); cudaFree(b->cstats); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
   cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
   policy_tc_free(b->tc);
   if (b->h_pin) cudaFreeHost(b->h_pin);
@@ -356,10 +373,11 @@ void tfode_batch_destroy(TfodeBatch* b) {
 int tfode_batch_set_stream(TfodeBatch* b, void* stream) { if (!b) return TFODE_EINVAL; b->stream = (cudaStream_t)stream; return TFODE_OK; }
 int tfode_batch_n_envs(const TfodeBatch* b) { return b ? b->cfg.n_envs : 0; }
 int64_t tfode_batch_launch_count(const TfodeBatch* b) { return b ? b->launches : 0; }
-int tfode_batch_sync(TfodeBatch* b) { if (!b) return TFODE_EINVAL; CK(cudaStreamSynchronize(b->stream)); return TFODE_OK; }
+int tfode_batch_sync(TfodeBatch* b) { if (!b) return TFODE_EINVAL; GUARD(b); CK(cudaStreamSynchronize(b->stream)); return TFODE_OK; }
 
 int tfode_batch_reset(TfodeBatch* b, const int32_t* env_ids, int n) {
   if (!b) return TFODE_EINVAL;
+  GUARD(b);
   if (!env_ids) return launch_reset(b, nullptr, b->cfg.n_envs, 0);
   if (n <= 0) return TFODE_OK;
   for (int i = 0; i < n; i++) if (env_ids[i] < 0 || env_ids[i] >= b->cfg.n_envs) { b->err = "env id out of range"; return TFODE_EINVAL; }
@@ -371,6 +389,7 @@ int tfode_batch_reset(TfodeBatch* b, const int32_t* env_ids, int n) {
 
 int tfode_batch_set_actions(TfodeBatch* b, const float* actions_dev) {
   if (!b || !actions_dev) return TFODE_EINVAL;
+  GUARD(b);
   const int n = b->cfg.n_envs;
   const float bmax = b->cfg.controller == TFODE_CTRL_CRAWLER ? b->cfg.crawler_amp : 25.0f;
   set_actions_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, actions_dev, bmax);
@@ -381,6 +400,7 @@ int tfode_batch_set_actions(TfodeBatch* b, const float* actions_dev) {
 
 int tfode_batch_set_speed(TfodeBatch* b, const float* speed_dev) {
   if (!b) return TFODE_EINVAL;
+  GUARD(b);
   if (!speed_dev) { b->P.ext_speed = nullptr; return TFODE_OK; }
   CK(cudaMemcpyAsync(b->ext_speed, speed_dev, sizeof(float) * (size_t)b->cfg.n_envs, cudaMemcpyDeviceToDevice, b->stream));
   b->P.ext_speed = b->ext_speed;
@@ -389,6 +409,7 @@ int tfode_batch_set_speed(TfodeBatch* b, const float* speed_dev) {
 
 int tfode_batch_load_policy(TfodeBatch* b, const float* w, size_t n_floats) {
   if (!b || !w) return TFODE_EINVAL;
+  GUARD(b);
   const size_t H = TFODE_MLP_HIDDEN, need = 17 * H + H + H * H + H + H * 2 + 2;
   if (n_floats != need) { b->err = "policy blob must hold 272898 floats (W1 b1 W2 b2 W3 b3)"; return TFODE_EINVAL; }
   if (!b->weights) CK(cudaMalloc(&b->weights, sizeof(float) * need));
@@ -396,6 +417,7 @@ int tfode_batch_load_policy(TfodeBatch* b, const float* w, size_t n_floats) {
   CK(cudaStreamSynchronize(b->stream));
   int rc = policy_tc_upload(b->tc, w, b->stream);
   if (rc != 0) { b->err = "policy_tc_upload failed"; return TFODE_ECUDA; }
+  b->P.policy_w = b->weights;
   b->has_policy = true;
   return TFODE_OK;
 }
@@ -404,9 +426,9 @@ static int run_policy(TfodeBatch* b, const float* in, const int* list, const int
   const size_t H = TFODE_MLP_HIDDEN;
   const float* W1 = b->weights; const float* b1 = W1 + 17 * H; const float* W2 = b1 + H; const float* b2 = W2 + H * H; const float* W3 = b2 + H; const float* b3 = W3 + H * 2;
   if (b->cfg.policy_precision == TFODE_POLICY_TC) {
-    int rc = policy_tc_launch(b->tc, in, list, n_list, m_direct, max_rows, b1, b2, W3, b3, b->rec, act_direct, b->stream);
+    const cudaError_t e = policy_tc_launch(b->tc, in, list, n_list, m_direct, max_rows, b1, b2, W3, b3, b->rec, act_direct, b->stream);
     b->launches += 1;
-    if (rc != 0) { b->err = std::string("policy_tc_launch: ") + cudaGetErrorString(cudaGetLastError()); return TFODE_ECUDA; }
+    if (e != cudaSuccess) { b->err = std::string("policy_tc_launch: ") + cudaGetErrorString(e); return TFODE_ECUDA; }
     return TFODE_OK;
   }
   const int blocks = (max_rows + POL_ROWS - 1) / POL_ROWS;
@@ -418,13 +440,18 @@ static int run_policy(TfodeBatch* b, const float* in, const int* list, const int
 
 int tfode_batch_step(TfodeBatch* b, int n_substeps) {
   if (!b || n_substeps < 0) return TFODE_EINVAL;
+  GUARD(b);
   if (n_substeps == 0) return TFODE_OK;
   const int n = b->cfg.n_envs;
   const bool mlp = b->cfg.controller == TFODE_CTRL_MLP, mtree = b->cfg.controller == TFODE_CTRL_MODEL_TREE;
   if (mlp && !b->has_policy) { b->err = "TFODE_CTRL_MLP needs tfode_batch_load_policy first"; return TFODE_ESTATE; }
   if (mtree && !b->has_trees) { b->err = "TFODE_CTRL_MODEL_TREE needs tfode_batch_load_model_trees first"; return TFODE_ESTATE; }
+  // TFODE_POLICY_FP32: the actor runs inside step_kernel at each environment's own IC tick (actor_fused), so a call is ONE launch.
+  // TFODE_POLICY_TC / model trees: environments park at their IC tick, the batched policy kernel serves the parked list, the next
+  // launch resumes them.
+  const bool fused_actor = mlp && b->cfg.policy_precision == TFODE_POLICY_FP32;
   int rounds = 1;
-  if (mlp || mtree) {
+  if ((mlp && !fused_actor) || mtree) {
     int period_steps = b->cfg.ic_period > 0 ? (int)std::floor(b->cfg.ic_period / b->cfg.dt) : 1;
     if (period_steps < 1) period_steps = 1;
     rounds = n_substeps / period_steps + 2;
@@ -435,7 +462,7 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
     step_kernel<<<(n + ENVS_PER_CTA - 1) / ENVS_PER_CTA, ENVS_PER_CTA * 32, b->smem_step, b->stream>>>(P);
     b->launches++;
     CK(cudaGetLastError());
-    if (mlp) {
+    if (mlp && !fused_actor) {
       int rc = run_policy(b, b->policy_in, b->parked_list, b->n_parked, 0, n, nullptr);
       if (rc != TFODE_OK) return rc;
       zero_int_kernel<<<1, 1, 0, b->stream>>>(b->n_parked);
@@ -454,6 +481,7 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
 
 int tfode_policy_infer(TfodeBatch* b, const float* obs_scaled_dev, int m, float* act_dev) {
   if (!b || !obs_scaled_dev || !act_dev || m < 0) return TFODE_EINVAL;
+  GUARD(b);
   if (!b->has_policy) { b->err = "no policy loaded"; return TFODE_ESTATE; }
   if (m == 0) return TFODE_OK;
   return run_policy(b, obs_scaled_dev, nullptr, nullptr, m, m, act_dev);
@@ -461,6 +489,7 @@ int tfode_policy_infer(TfodeBatch* b, const float* obs_scaled_dev, int m, float*
 
 int tfode_batch_observe(TfodeBatch* b, float* obs17, float* reward, uint8_t* done, int32_t* contact_count) {
   if (!b) return TFODE_EINVAL;
+  GUARD(b);
   const int n = b->cfg.n_envs;
   observe_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, obs17, reward, done, contact_count);
   b->launches++;
@@ -468,8 +497,19 @@ int tfode_batch_observe(TfodeBatch* b, float* obs17, float* reward, uint8_t* don
   return TFODE_OK;
 }
 
+int tfode_batch_pack_rollout(TfodeBatch* b, float* rows_dev) {
+  if (!b || !rows_dev) return TFODE_EINVAL;
+  GUARD(b);
+  const int n = b->cfg.n_envs;
+  pack_rollout_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, b->cfg.env_id_offset, rows_dev);
+  b->launches++;
+  CK(cudaGetLastError());
+  return TFODE_OK;
+}
+
 int tfode_batch_get_bodies(TfodeBatch* b, float* out_dev) {
   if (!b || !out_dev) return TFODE_EINVAL;
+  GUARD(b);
   const int n = b->cfg.n_envs * NB;
   bodies_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, b->cfg.n_envs, out_dev);
   b->launches++;
@@ -477,21 +517,40 @@ int tfode_batch_get_bodies(TfodeBatch* b, float* out_dev) {
   return TFODE_OK;
 }
 
-int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, int* n_rows_host) {
-  if (!b || !n_rows_host) return TFODE_EINVAL;
+int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, int* n_rows_host, int* n_dropped_host) {
+  if (!b || !n_rows_host || max_rows < 0) return TFODE_EINVAL;
+  GUARD(b);
   int cnt = 0;
   CK(cudaMemcpyAsync(&cnt, b->n_trans, sizeof(int), cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
-  int avail = cnt < b->trans_cap ? cnt : b->trans_cap;
-  int take = avail < max_rows ? avail : max_rows;
-  if (out_dev && take > 0) CK(cudaMemcpyAsync(out_dev, b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)take, cudaMemcpyDeviceToDevice, b->stream));
+  const int avail = cnt < b->trans_cap ? cnt : b->trans_cap;   // rows held by the ring
+  if (n_dropped_host) *n_dropped_host = cnt - avail;             // produced beyond transition_capacity since the last drain: lost
+  if (avail > max_rows || (avail > 0 && !out_dev)) {             // nothing is consumed: the caller retries with room for *n_rows_host rows
+    *n_rows_host = avail;
+    b->err = "tfode_batch_drain_transitions: " + std::to_string(avail) + " rows pending, buffer holds " + std::to_string(max_rows);
+    return TFODE_EINVAL;
+  }
+  if (avail > 0) CK(cudaMemcpyAsync(out_dev, b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)avail, cudaMemcpyDeviceToDevice, b->stream));
   CK(cudaMemsetAsync(b->n_trans, 0, sizeof(int), b->stream));
-  *n_rows_host = cnt;  // rows produced (rows beyond the ring capacity were dropped)
+  *n_rows_host = avail;   // rows written to out_dev
+  return TFODE_OK;
+}
+
+int tfode_batch_contact_stats(TfodeBatch* b, int64_t* over_capacity_steps, int64_t* max_generated, int reset) {
+  if (!b) return TFODE_EINVAL;
+  GUARD(b);
+  unsigned long long h[2] = {0, 0};
+  CK(cudaMemcpyAsync(h, b->cstats, sizeof(h), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  if (over_capacity_steps) *over_capacity_steps = (int64_t)h[0];
+  if (max_generated) *max_generated = (int64_t)h[1];
+  if (reset) CK(cudaMemsetAsync(b->cstats, 0, sizeof(h), b->stream));
   return TFODE_OK;
 }
 
 int tfode_batch_rollout_host(TfodeBatch* b, const float* actions_host, int n_substeps, float* obs17_host, float* reward_host, uint8_t* done_host) {
   if (!b) return TFODE_EINVAL;
+  GUARD(b);
   const int n = b->cfg.n_envs;
   float* pin_act = b->h_pin; float* pin_obs = pin_act + 2 * (size_t)n; float* pin_rew = pin_obs + 17 * (size_t)n; uint8_t* pin_done = (uint8_t*)(pin_rew + n);
   if (actions_host) {
@@ -513,6 +572,7 @@ int tfode_batch_rollout_host(TfodeBatch* b, const float* actions_host, int n_sub
 
 int tfode_batch_get_state(TfodeBatch* b, int env, TfodeEnvState* s) {
   if (!b || !s || env < 0 || env >= b->cfg.n_envs) return TFODE_EINVAL;
+  GUARD(b);
   EnvRec r;
   CK(cudaMemcpyAsync(&r, b->rec + env, sizeof(EnvRec), cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
@@ -540,6 +600,7 @@ int tfode_batch_get_state(TfodeBatch* b, int env, TfodeEnvState* s) {
 
 int tfode_batch_set_state(TfodeBatch* b, int env, const TfodeEnvState* s) {
   if (!b || !s || env < 0 || env >= b->cfg.n_envs) return TFODE_EINVAL;
+  GUARD(b);
   EnvRec r;
   CK(cudaMemcpyAsync(&r, b->rec + env, sizeof(EnvRec), cudaMemcpyDeviceToHost, b->stream));
   CK(cudaStreamSynchronize(b->stream));
@@ -586,6 +647,7 @@ int tfode_model_tree_parse(const char* yaml_text, size_t len, int oblique, Tfode
 
 int tfode_batch_load_model_trees(TfodeBatch* b, const char* yaml_1, size_t len_1, const char* yaml_2, size_t len_2, int oblique, int degree, int interaction_only) {
   if (!b) return TFODE_EINVAL;
+  GUARD(b);
   if (!yaml_1 || !yaml_2) { b->err = "null argument"; return TFODE_EINVAL; }
   if (degree < 1 || degree > 2) { b->err = "model tree degree must be 1 (Linear_model_tree) or 2 (Polynomial_model_tree)"; return TFODE_EINVAL; }
   const int nf = tfode_fmt::poly_feature_count(TFODE_TREE_INPUTS, degree, interaction_only != 0);
@@ -604,7 +666,6 @@ int tfode_batch_load_model_trees(TfodeBatch* b, const char* yaml_1, size_t len_1
         }
       }
   } catch (const std::exception& e) { b->err = e.what(); return TFODE_EINVAL; }
-  CK(cudaSetDevice(b->cfg.device));
   CK(cudaStreamSynchronize(b->stream));
   for (int k = 0; k < 2; k++) {
     cudaFree(b->tree_nodes[k]); cudaFree(b->tree_params[k]); b->tree_nodes[k] = nullptr; b->tree_params[k] = nullptr;
@@ -621,6 +682,7 @@ int tfode_batch_load_model_trees(TfodeBatch* b, const char* yaml_1, size_t len_1
 
 int tfode_model_tree_infer(TfodeBatch* b, const double* state_dev, int m, double* act_dev, int32_t* node_dev) {
   if (!b || !state_dev || !act_dev || m < 0) return TFODE_EINVAL;
+  GUARD(b);
   if (!b->has_trees) { b->err = "no model trees loaded"; return TFODE_ESTATE; }
   if (m == 0) return TFODE_OK;
   const int blocks = std::min((m + 127) / 128, 148 * 8);
@@ -632,6 +694,7 @@ int tfode_model_tree_infer(TfodeBatch* b, const double* state_dev, int m, double
 
 int tfode_batch_get_tree_nodes(TfodeBatch* b, int32_t* out_dev) {
   if (!b || !out_dev) return TFODE_EINVAL;
+  GUARD(b);
   const int n = b->cfg.n_envs;
   tree_nodes_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->rec, n, out_dev);
   b->launches++;

@@ -104,8 +104,12 @@ struct StepParams {
   float* policy_in;        // [n_envs,17] scaled observations of parked envs
   int* parked_list;        // env ids parked in this launch
   int* n_parked;
+  const float* policy_w;   // fp32 actor blob W1 b1 W2 b2 W3 b3 (TFODE_POLICY_FP32: the actor runs inside step_kernel)
   // transitions
   float* trans; int trans_cap; int* n_trans;
+  // contact-capacity audit: [0] sub-steps in which an environment generated more contacts than max_contacts (the excess is
+  // dropped), [1] largest number of contacts one environment generated in one sub-step
+  unsigned long long* cstats;
   // external commands
   const float* ext_speed;  // NULL or [n_envs]
   // tire-sphere centres in the wheel frame (Model::ring, padded to float4) in global memory: the lanes of a warp read 32

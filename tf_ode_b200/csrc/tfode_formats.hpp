@@ -244,7 +244,8 @@ inline std::map<int, YamlNodeEntry> parse_tree_yaml(const char* text, size_t len
 }
 
 // Linear_model_tree::_build_tree_recursively (model_tree.cc:21-45): ids are handed out by _new_node() in visiting order.
-inline void build_flat(const std::map<int, YamlNodeEntry>& y, bool oblique, FlatTree& out, int node_index, int& node_count) {
+inline void build_flat(const std::map<int, YamlNodeEntry>& y, bool oblique, FlatTree& out, int node_index, int& node_count, int depth = 0) {
+  if (depth > 2048) throw std::runtime_error("model tree YAML: tree deeper than 2048 levels");   // bounds the recursion on chain-shaped input
   const int id = out.nodes[node_index].id;
   auto it = y.find(id);
   if (it == y.end() || !it->second.has_terminal) throw std::runtime_error("model tree YAML: node " + std::to_string(id) + " has no 'terminal' field");
@@ -265,7 +266,7 @@ inline void build_flat(const std::map<int, YamlNodeEntry>& y, bool oblique, Flat
     out.nodes.push_back(nn);
     const int ci = (int)out.nodes.size() - 1;
     out.nodes[node_index].child[child] = ci;
-    build_flat(y, oblique, out, ci, node_count);
+    build_flat(y, oblique, out, ci, node_count, depth + 1);
   }
 }
 
@@ -334,7 +335,7 @@ struct Bundle { int num_shards = 1; std::map<std::string, BundleEntry> entries; 
 // visit(key, value bytes) for every entry, undoing the shared-prefix key compression.
 template <class F>
 inline void table_block(const std::vector<unsigned char>& file, uint64_t off, uint64_t size, F&& visit) {
-  if (off + size + 5 > file.size() || size < 4) throw std::runtime_error("tensor bundle index: block handle outside the file");
+  if (size < 4 || size > file.size() || file.size() - size < 5 || off > file.size() - size - 5) throw std::runtime_error("tensor bundle index: block handle outside the file");
   if (file[off + size] != 0) throw std::runtime_error("tensor bundle index: compressed block (type " + std::to_string((int)file[off + size]) + "); BundleWriter writes uncompressed tables");
   if (le32(&file[off + size + 1]) != crc32c_mask(crc32c(&file[off], size + 1))) throw std::runtime_error("tensor bundle index: block checksum mismatch");
   const uint32_t n_restarts = le32(&file[off + size - 4]);

@@ -112,6 +112,53 @@ __device__ void get_state17(const WarpSm& S, float* s) {
   for (int i = 0; i < 12; i++) s[5 + i] = S.c.ft[i];
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fused actor (TF_model<float>::infer, tf_cpp_binding.cc:70-113; 17 -> 512 relu -> 512 relu -> 2 tanh of
+// scripts/rover_training_1.py:26-35) for ONE environment, run by the environment's own warp at its IC tick.
+// Lane l owns hidden units l, l+32, ..., l+480: 16 independent accumulators per lane, each summed in input order
+// starting from the bias with one fma per weight -- the order of policy_fp32_kernel and of the oracle, so the
+// result is bit-identical to both.  Weights stream from L2 (1.09 MB, shared by every environment of the GPU) with
+// fully coalesced 128-byte rows; inputs and hidden activations sit in the environment's row scratch (dead
+// between the sweeps and the next sub-step's row build) and are read as shared-memory broadcasts.
+// Cost: 8.7 k fma + 8.7 k coalesced loads per lane, once per 0.5 s of simulated time (every 500 sub-steps).
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float* actor_scratch(WarpSm& S) { return &S.rowJ[0][0]; }   // [0..17) inputs / outputs, [32..544) h1, [544..1056) h2
+static_assert(sizeof(float) * MAXROWS * 12 >= sizeof(float) * (32 + 2 * TFODE_MLP_HIDDEN), "actor scratch aliases the row array");
+__device__ __noinline__ void actor_fused(WarpSm& S, const float* __restrict__ w, int lane) {
+  constexpr int H = TFODE_MLP_HIDDEN, U = H / 32;
+  const float* W1 = w; const float* b1 = W1 + 17 * H; const float* W2 = b1 + H; const float* b2 = W2 + H * H;
+  const float* W3 = b2 + H; const float* b3 = W3 + H * 2;
+  float* x = actor_scratch(S); float* h1 = x + 32; float* h2 = h1 + H;
+  float acc[U];
+#pragma unroll
+  for (int u = 0; u < U; u++) acc[u] = __ldg(b1 + lane + 32 * u);
+  for (int i = 0; i < 17; i++) {
+    const float xi = x[i];
+#pragma unroll
+    for (int u = 0; u < U; u++) acc[u] = tfn::fma(xi, __ldg(W1 + i * H + lane + 32 * u), acc[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < U; u++) h1[lane + 32 * u] = acc[u] > 0 ? acc[u] : 0;
+  __syncwarp();
+#pragma unroll
+  for (int u = 0; u < U; u++) acc[u] = __ldg(b2 + lane + 32 * u);
+#pragma unroll 2
+  for (int i = 0; i < H; i++) {
+    const float hi = h1[i];
+#pragma unroll
+    for (int u = 0; u < U; u++) acc[u] = tfn::fma(hi, __ldg(W2 + i * H + lane + 32 * u), acc[u]);
+  }
+#pragma unroll
+  for (int u = 0; u < U; u++) h2[lane + 32 * u] = acc[u] > 0 ? acc[u] : 0;
+  __syncwarp();
+  if (lane < 2) {   // output layer: one lane per action, accumulated in input order from the bias
+    float s3 = __ldg(b3 + lane);
+    for (int i = 0; i < H; i++) s3 = tfn::fma(h2[i], __ldg(W3 + i * 2 + lane), s3);
+    x[lane] = tfn::tanh(s3);
+  }
+  __syncwarp();
+}
+
 // ================================================================================================
 //                                         THE STEP KERNEL
 // One CTA = ENVS_PER_CTA environments.  Collision, row construction, integration and the rover's control
@@ -179,9 +226,14 @@ __device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const f
   const int row = entry & 127;
   const float2* Jp = reinterpret_cast<const float2*>(&S.rowJ[row][(entry & BR_IS1) ? 0 : 6]);
   const float2 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
+#ifdef TFODE_ROWS_AOS
   const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);       // rhs Ad Adcfm lo
   const float2 s1 = *reinterpret_cast<const float2*>(&S.rowS[row][RS_HI]);   // hi lambda
   static_assert(RS_LAM == RS_HI + 1 && (RS_HI % 2) == 0, "hi and lambda travel in one 8-byte load");
+#else
+  const float4 s0 = S.rowC[row];    // rhs Ad Adcfm lo
+  const float2 s1 = S.rowHL[row];   // hi lambda
+#endif
   r.meta = entry;
   r.hi = s1.x; lam = s1.y;
   r.J[0] = j0.x; r.J[1] = j0.y; r.J[2] = j1.x; r.J[3] = j1.y; r.J[4] = j2.x; r.J[5] = j2.y;
@@ -206,8 +258,8 @@ __device__ __forceinline__ void pair_barrier(int p) { asm volatile("bar.sync %0,
 // header slots (RS_HDR is dead once the order is built), written by the pair's helper warp while the sweeps of block 0 run.
 __device__ __forceinline__ unsigned char* ord_buffer(WarpSm& S, int off, int r, int& stride) {
   if (r == 0) { stride = 1; return S.order + off; }
-  stride = (int)sizeof(S.rowS[0]);
-  return reinterpret_cast<unsigned char*>(&S.rowS[off][RS_HDR]) + (r == 1 ? 0 : 1);
+  stride = ROW_HDR_STRIDE;
+  return reinterpret_cast<unsigned char*>(&ROWF(S, off, HDR)) + (r == 1 ? 0 : 1);
 }
 // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt on this island's slice of the environment's stream (one lane).
 // The draw of the next swap (LCG step, bit folds, reciprocal-multiply modulo) overlaps the shared-memory round trip of this one.
@@ -247,11 +299,11 @@ __device__ __forceinline__ void pgs_fill_sched(const WarpSm& S, const unsigned c
   int k = 0;
   for (; k + 4 <= m; k += 4) {
     const int r0 = ord[k * ostride], r1 = ord[(k + 1) * ostride], r2 = ord[(k + 2) * ostride], r3 = ord[(k + 3) * ostride];
-    const int p0 = __float_as_int(S.rowS[r0][RS_ENT]), p1 = __float_as_int(S.rowS[r1][RS_ENT]);
-    const int p2 = __float_as_int(S.rowS[r2][RS_ENT]), p3 = __float_as_int(S.rowS[r3][RS_ENT]);
+    const int p0 = __float_as_int(ROWF(S, r0, ENT)), p1 = __float_as_int(ROWF(S, r1, ENT));
+    const int p2 = __float_as_int(ROWF(S, r2, ENT)), p3 = __float_as_int(ROWF(S, r3, ENT));
     pgs_push(qw, p0, b); pgs_push(qw, p1, b); pgs_push(qw, p2, b); pgs_push(qw, p3, b);
   }
-  for (; k < m; k++) pgs_push(qw, __float_as_int(S.rowS[ord[k * ostride]][RS_ENT]), b);
+  for (; k < m; k++) pgs_push(qw, __float_as_int(ROWF(S, ord[k * ostride], ENT)), b);
   __syncwarp();
   mask0 = 0ull; T = 0;
   int cur = 0, ent = qn > 0 ? (int)myq[0] : dummy_ent;
@@ -271,7 +323,7 @@ __device__ __forceinline__ void pgs_fill_sched(const WarpSm& S, const unsigned c
 __device__ __forceinline__ void pgs_queue_extent(const WarpSm& S, const unsigned char* ordA, int m, int b, int& qn, int& qoff) {
   qn = 0;
   for (int k = 0; k < m; k++) {
-    const int pk = __float_as_int(S.rowS[ordA[k]][RS_ENT]);
+    const int pk = __float_as_int(ROWF(S, ordA[k], ENT));
     if (((pk >> 24) & 15) == b || ((pk >> 8) & 15) == b) qn++;
   }
   int incl = qn;
@@ -280,10 +332,32 @@ __device__ __forceinline__ void pgs_queue_extent(const WarpSm& S, const unsigned
   qoff = incl - qn;
 }
 
+// Which environment slot of the CTA half `lane >> 4` of pair `pair` works on.  Default: slots 2*pair, 2*pair + 1.
+// -DTFODE_SORT_PAIRS: the CTA's environments are ranked by their row count of this sub-step and pair p takes ranks 2p and
+// 2p + 1, so that a sweep warp's two environments need about the same number of lock-steps per sweep (the warp runs
+// max(T_a, T_b) of them: pairing like with like minimises the lock-steps the CTA issues in total; the longest environment
+// sets the phase's length either way).  Sweep warp and helper warp of a pair evaluate the same ranking.
+__device__ __forceinline__ int pgs_env_of(const WarpSm* sm, int pair, int lane) {
+#ifdef TFODE_SORT_PAIRS
+  int w = 0;
+  if (lane < ENVS_PER_CTA) w = sm[lane].pgs_on ? sm[lane].c.n_rows : 0;
+  int rank = 0;
+#pragma unroll
+  for (int j = 0; j < ENVS_PER_CTA; j++) { const int wj = __shfl_sync(FULLMASK, w, j); rank += (wj > w || (wj == w && j < lane)) ? 1 : 0; }
+  const int want = 2 * pair + (lane >> 4);
+  int e = 0;
+#pragma unroll
+  for (int j = 0; j < ENVS_PER_CTA; j++) { const int rj = __shfl_sync(FULLMASK, rank, j); if (rj == want) e = j; }
+  return e;
+#else
+  return 2 * pair + (lane >> 4);
+#endif
+}
+
 // Helper warp of pair p: everything reorders 1 and 2 need that does not depend on the solve -- permutation, queues, firing
 // schedule -- for the pair's two environments, handed to the sweep warp at two meetings of the pair's named barrier.
 __device__ void pgs_helper(WarpSm* sm, int pgs_iters, int p, int lane) {
-  const int e = 2 * p + (lane >> 4), b = lane & 15, hbase = lane & 16;
+  const int e = pgs_env_of(sm, p, lane), b = lane & 15, hbase = lane & 16;
   WarpSm& S = sm[e];
   const bool on = S.pgs_on != 0 && b < NB;
   int off = 0, m = 0, base = 0; bool leader = false;
@@ -320,7 +394,7 @@ __device__ void pgs_helper(WarpSm* sm, int pgs_iters, int p, int lane) {
 }
 
 __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
-  const int e = 2 * wid + (lane >> 4), b = lane & 15;
+  const int e = pgs_env_of(sm, wid, lane), b = lane & 15;
   int hbase = lane & 16;
   asm volatile("" : "+r"(hbase));   // (same reason as s_addr below)
   // The environment's shared-memory address is made opaque: under the 128-register cap ptxas otherwise rematerialises it
@@ -394,14 +468,14 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       {
         const int e0 = (mask32 & 1u) ? (int)myq[0] : dummy_ent;
         pgs_load_row(S, e0, iI, rb, lam);
-        lamf = S.rowS[(e0 & 127) - ((e0 >> 13) & 3)][RS_LAM];
+        lamf = ROWF(S, (e0 & 127) - ((e0 >> 13) & 3), LAM);
       }
       // one lock-step: `fire` = this lane relaxes rb now; `en` = its queue entry for the next lock-step
       auto lock_step = [&](const bool fire, const int en) {
         BodyRow rn; float lam_n, lamf_n;
         pgs_load_row(S, en, iI, rn, lam_n);
         const int nrow_n = (en & 127) - ((en >> 13) & 3);
-        lamf_n = S.rowS[nrow_n][RS_LAM];
+        lamf_n = ROWF(S, nrow_n, LAM);
         const int row = rb.meta & 127, pl = hbase | ((rb.meta >> 8) & 15);
         const bool is1 = (rb.meta & BR_IS1) != 0, solo = (rb.meta & BR_SOLO) != 0, fric = (rb.meta >> 13) != 0;
         const float part = tfn::dot6(rb.J, fc);
@@ -416,7 +490,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         float nl = lam_c + delta;
         if (nl < lo) { delta = lo - lam_c; nl = lo; }
         else if (nl > hi) { delta = hi - lam_c; nl = hi; }
-        if (fire && is1) S.rowS[row][RS_LAM] = nl;
+        if (fire && is1) ROWF(S, row, LAM) = nl;
         const float dm = delta * invM;
         const float f0 = tfn::fma(dm, rb.J[0], fc[0]), f1 = tfn::fma(dm, rb.J[1], fc[1]), f2 = tfn::fma(dm, rb.J[2], fc[2]);
         const float f3 = tfn::fma(delta, rb.a[0], fc[3]), f4 = tfn::fma(delta, rb.a[1], fc[4]), f5 = tfn::fma(delta, rb.a[2], fc[5]);
@@ -453,7 +527,7 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
     rb.a[0] = 0; rb.a[1] = 0; rb.a[2] = 0;
     float lam = 0.0f;
     if (qn > 0) pgs_load_row(S, myq[0], iI, rb, lam);
-    float lamf = S.rowS[(rb.meta & 127) - ((rb.meta >> 13) & 3)][RS_LAM];
+    float lamf = ROWF(S, (rb.meta & 127) - ((rb.meta >> 13) & 3), LAM);
     int ent_next = (qn > 1) ? myq[1] : rb.meta;
     while (__any_sync(FULLMASK, cur < qn)) {
       const bool have = cur < qn;
@@ -475,14 +549,14 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       if (nl < lo) { delta = lo - lam_c; nl = lo; }
       else if (nl > hi) { delta = hi - lam_c; nl = hi; }
       if (ready) {
-        if (is1) S.rowS[row][RS_LAM] = nl;
+        if (is1) ROWF(S, row, LAM) = nl;
         const float dm = delta * invM;
         fc[0] = tfn::fma(dm, rb.J[0], fc[0]); fc[1] = tfn::fma(dm, rb.J[1], fc[1]); fc[2] = tfn::fma(dm, rb.J[2], fc[2]);
         fc[3] = tfn::fma(delta, rb.a[0], fc[3]); fc[4] = tfn::fma(delta, rb.a[1], fc[4]); fc[5] = tfn::fma(delta, rb.a[2], fc[5]);
         cur++;
         if (cur < qn) {
           pgs_load_row(S, ent_next, iI, rb, lam);
-          lamf = S.rowS[(ent_next & 127) - ((ent_next >> 13) & 3)][RS_LAM];   // after the store above: sees a normal row relaxed just now
+          lamf = ROWF(S, (ent_next & 127) - ((ent_next >> 13) & 3), LAM);   // after the store above: sees a normal row relaxed just now
           if (cur + 1 < qn) ent_next = myq[cur + 1];
         }
       }
@@ -518,7 +592,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
 
   int budget = 0;
   if (valid) budget = (P.set_budget >= 0) ? P.set_budget : P.budget[env];
-  if (lane == 0) { S.pgs_on = 0; S.c.frozen = 0; S.c.parked = 0; }
+  if (lane == 0) { S.pgs_on = 0; S.c.frozen = 0; S.c.parked = 0; S.cap_over = 0; S.cap_max = 0; }
 
   // ---------------------------------------------------------------- load the record (coalesced float4 -> smem staging -> registers)
   EnvRec* grec = P.rec + (valid ? env : 0);
@@ -744,7 +818,12 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
       }
       if (__any_sync(FULLMASK, fork_hit != 0) && lane == 0) S.c.fork_collision = 1;
       const int nc = min(nc_total, maxc);
-      if (lane == 0) S.c.n_contacts = nc_total;
+      if (lane == 0) {
+        S.c.n_contacts = nc_total;
+        // capacity audit (the reference creates every contact, ode/environment.cc:101-128): tfode_batch_contact_stats reports these
+        if (nc_total > maxc) S.cap_over++;
+        if (nc_total > S.cap_max) S.cap_max = nc_total;
+      }
       __syncwarp();
 
       PT_MARK(0)
@@ -826,9 +905,9 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
           float* Jr = S.rowJ[jrow0 + r];
 #pragma unroll
           for (int k = 0; k < 12; k++) Jr[k] = 0.0f;
-          float* Sr = S.rowS[jrow0 + r];
-          Sr[RS_C] = 0.0f; Sr[RS_ADCFM] = cfg.cfm; Sr[RS_LO] = -CUDART_INF_F; Sr[RS_HI] = CUDART_INF_F; Sr[RS_LAM] = 0.0f;
-          Sr[RS_HDR] = __int_as_float(hdr);
+          const int Sr = jrow0 + r;
+          ROWF(S, Sr, C) = 0.0f; ROWF(S, Sr, ADCFM) = cfg.cfm; ROWF(S, Sr, LO) = -CUDART_INF_F; ROWF(S, Sr, HI) = CUDART_INF_F; ROWF(S, Sr, LAM) = 0.0f;
+          ROWF(S, Sr, HDR) = __int_as_float(hdr);
         }
         if (!M.jslider[j]) {
           // ball part (setBall)
@@ -837,7 +916,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
           for (int r = 0; r < 3; r++) {
             float* Jr = S.rowJ[jrow0 + r];
             Jr[r] = 1.0f; Jr[6 + r] = -1.0f;
-            S.rowS[jrow0 + r][RS_C] = k_erp * (a2[r] + x2[r] - a1[r] - x1[r]);
+            ROWF(S, jrow0 + r, C) = k_erp * (a2[r] + x2[r] - a1[r] - x1[r]);
           }
           { float* J0 = S.rowJ[jrow0 + 0]; float* J1 = S.rowJ[jrow0 + 1]; float* J2 = S.rowJ[jrow0 + 2];
             J0[4] = a1[2]; J0[5] = -a1[1]; J1[3] = -a1[2]; J1[5] = a1[0]; J2[3] = a1[1]; J2[4] = -a1[0];
@@ -848,14 +927,14 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
           cross3(bb, ax1, ax2);
           { float* J3 = S.rowJ[jrow0 + 3]; float* J4 = S.rowJ[jrow0 + 4];
             for (int k = 0; k < 3; k++) { J3[3 + k] = pp[k]; J3[9 + k] = -pp[k]; J4[3 + k] = qq[k]; J4[9 + k] = -qq[k]; }
-            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(bb, pp); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(bb, qq); }
+            ROWF(S, jrow0 + 3, C) = k_erp * dot3(bb, pp); ROWF(S, jrow0 + 4, C) = k_erp * dot3(bb, qq); }
           if (jm == 6) {
-            float* J5 = S.rowJ[jrow0 + 5]; float* S5 = S.rowS[jrow0 + 5];
+            float* J5 = S.rowJ[jrow0 + 5]; const int S5 = jrow0 + 5;
             for (int k = 0; k < 3; k++) { J5[3 + k] = ax1[k]; J5[9 + k] = -ax1[k]; }
             if (jlimit) {  // unpowered joint at a stop (the boggie hinge)
-              S5[RS_C] = -k_erp * jlimit_err;
-              if (jlimit == 1) { S5[RS_LO] = 0.0f; S5[RS_HI] = CUDART_INF_F; } else { S5[RS_LO] = -CUDART_INF_F; S5[RS_HI] = 0.0f; }
-            } else { S5[RS_C] = jvel; S5[RS_LO] = -jfmax; S5[RS_HI] = jfmax; }
+              ROWF(S, S5, C) = -k_erp * jlimit_err;
+              if (jlimit == 1) { ROWF(S, S5, LO) = 0.0f; ROWF(S, S5, HI) = CUDART_INF_F; } else { ROWF(S, S5, LO) = -CUDART_INF_F; ROWF(S, S5, HI) = 0.0f; }
+            } else { ROWF(S, S5, C) = jvel; ROWF(S, S5, LO) = -jfmax; ROWF(S, S5, HI) = jfmax; }
           }
         } else {
           // slider: battery clamp (two bodies) or step fix (body - world)
@@ -869,7 +948,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
           for (int r = 0; r < 3; r++) {
             float* Jr = S.rowJ[jrow0 + r];
             Jr[3 + r] = 1.0f; if (has2) Jr[9 + r] = -1.0f;
-            S.rowS[jrow0 + r][RS_C] = 2 * k_erp * e[r];
+            ROWF(S, jrow0 + r, C) = 2 * k_erp * e[r];
           }
           float ax1[3], pp[3], qq[3];
           mulRv(ax1, R1, M.axis1[j]);
@@ -885,7 +964,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
             for (int k = 0; k < 3; k++) { J3[6 + k] = -pp[k]; J4[6 + k] = -qq[k]; }
             float ofs[3]; mulRv(ofs, R2, offs);
             float cc[3] = {cvec[0] + ofs[0], cvec[1] + ofs[1], cvec[2] + ofs[2]};
-            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(pp, cc); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(qq, cc);
+            ROWF(S, jrow0 + 3, C) = k_erp * dot3(pp, cc); ROWF(S, jrow0 + 4, C) = k_erp * dot3(qq, cc);
             float qv[3] = {x1[0] - ofs[0] - x2[0], x1[1] - ofs[1] - x2[1], x1[2] - ofs[2] - x2[2]};
             posn = dot3(ax1, qv);
             // limit row with linear torque decoupling
@@ -894,13 +973,13 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
             for (int k = 0; k < 3; k++) { J5[k] = ax1[k]; J5[6 + k] = -ax1[k]; J5[3 + k] = ltd[k]; J5[9 + k] = ltd[k]; }
           } else {
             float ofs[3] = {offs[0] - x1[0], offs[1] - x1[1], offs[2] - x1[2]};
-            S.rowS[jrow0 + 3][RS_C] = k_erp * dot3(pp, ofs); S.rowS[jrow0 + 4][RS_C] = k_erp * dot3(qq, ofs);
+            ROWF(S, jrow0 + 3, C) = k_erp * dot3(pp, ofs); ROWF(S, jrow0 + 4, C) = k_erp * dot3(qq, ofs);
             float qv[3] = {x1[0] - offs[0], x1[1] - offs[1], x1[2] - offs[2]};
             posn = dot3(ax1, qv);
             for (int k = 0; k < 3; k++) J5[k] = ax1[k];
           }
           for (int k = 0; k < 3; k++) { J3[k] = pp[k]; J4[k] = qq[k]; }
-          S.rowS[jrow0 + 5][RS_C] = -k_erp * posn;  // lo = hi = 0: equality, unbounded
+          ROWF(S, jrow0 + 5, C) = -k_erp * posn;  // lo = hi = 0: equality, unbounded
         }
       }
       // ------------------------------------------------------------ contact rows (lane c = contact c), dxJointContact::getInfo2
@@ -920,22 +999,22 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
 #pragma unroll
         for (int r = 0; r < 3; r++) {
           const float* d = (r == 0) ? n : (r == 1 ? t1 : t2);
-          float* Jr = S.rowJ[r0 + r]; float* Sr = S.rowS[r0 + r];
+          float* Jr = S.rowJ[r0 + r]; const int Sr = r0 + r;
           float x[3]; cross3(x, c1, d);
           Jr[0] = d[0]; Jr[1] = d[1]; Jr[2] = d[2]; Jr[3] = x[0]; Jr[4] = x[1]; Jr[5] = x[2];
           if (has2) { cross3(x, c2, d); Jr[6] = -d[0]; Jr[7] = -d[1]; Jr[8] = -d[2]; Jr[9] = -x[0]; Jr[10] = -x[1]; Jr[11] = -x[2]; }
           else { Jr[6] = 0; Jr[7] = 0; Jr[8] = 0; Jr[9] = 0; Jr[10] = 0; Jr[11] = 0; }
-          Sr[RS_LAM] = 0.0f;
-          if (r == 0) { Sr[RS_C] = fps * erp_ * depth; Sr[RS_ADCFM] = soft ? 0.005f : cfg.cfm; Sr[RS_LO] = 0.0f; Sr[RS_HI] = CUDART_INF_F; Sr[RS_HDR] = __int_as_float(b1 | (b2 << 4) | (255 << 8)); }
-          else { Sr[RS_C] = 0.0f; Sr[RS_ADCFM] = cfg.cfm; Sr[RS_LO] = -cfg.mu; Sr[RS_HI] = cfg.mu; Sr[RS_HDR] = __int_as_float(b1 | (b2 << 4) | (r0 << 8)); }
+          ROWF(S, Sr, LAM) = 0.0f;
+          if (r == 0) { ROWF(S, Sr, C) = fps * erp_ * depth; ROWF(S, Sr, ADCFM) = soft ? 0.005f : cfg.cfm; ROWF(S, Sr, LO) = 0.0f; ROWF(S, Sr, HI) = CUDART_INF_F; ROWF(S, Sr, HDR) = __int_as_float(b1 | (b2 << 4) | (255 << 8)); }
+          else { ROWF(S, Sr, C) = 0.0f; ROWF(S, Sr, ADCFM) = cfg.cfm; ROWF(S, Sr, LO) = -cfg.mu; ROWF(S, Sr, HI) = cfg.mu; ROWF(S, Sr, HDR) = __int_as_float(b1 | (b2 << 4) | (r0 << 8)); }
         }
       }
       __syncwarp();
 
       // ------------------------------------------------------------ rhs, Ad (lane = row)
       for (int r = lane; r < m_total; r += 32) {
-        const float* Jr = S.rowJ[r]; float* Sr = S.rowS[r];
-        const int hdr = __float_as_int(Sr[RS_HDR]);
+        const float* Jr = S.rowJ[r];
+        const int hdr = __float_as_int(ROWF(S, r, HDR));
         const int b1 = hdr & 15, b2 = (hdr >> 4) & 15;
         const float* t1 = S.btmp[b1]; const float* i1 = S.binvI[b1];
         float s = tfn::dot6(Jr, t1);
@@ -947,13 +1026,13 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
           symMulV(a3, i2, Jr + 9);
           diag = diag + tfn::fma(i2[6], dot3(Jr + 6, Jr + 6), dot3(a3, Jr + 9));
         }
-        const float cfm_h = Sr[RS_ADCFM] * fps;
+        const float cfm_h = ROWF(S, r, ADCFM) * fps;
         const float Ad = cfg.sor_w / (diag + cfm_h);
-        Sr[RS_RHS] = tfn::fma(Sr[RS_C], fps, -s);
-        Sr[RS_AD] = Ad;
-        Sr[RS_ADCFM] = Ad * cfm_h;
+        ROWF(S, r, RHS) = tfn::fma(ROWF(S, r, C), fps, -s);
+        ROWF(S, r, AD) = Ad;
+        ROWF(S, r, ADCFM) = Ad * cfm_h;
         // c is consumed: its slot now holds the row's two pre-decoded sweep-queue entries (body 1's lane | body 2's lane << 16)
-        Sr[RS_ENT] = __int_as_float(pgs_make_entry(r, hdr, b1) | ((b2 < NB ? pgs_make_entry(r, hdr, b2) : (b1 << 8)) << 16));
+        ROWF(S, r, ENT) = __int_as_float(pgs_make_entry(r, hdr, b1) | ((b2 < NB ? pgs_make_entry(r, hdr, b2) : (b1 << 8)) << 16));
       }
 
       // ------------------------------------------------------------ constraint order per island (quickstep.cpp SOR_LCP)
@@ -963,7 +1042,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
       for (int r0 = 0; r0 < m_total; r0 += 32) {
         const int r = r0 + lane; const bool valid = r < m_total;
         int lab = -1, fric = 0;
-        if (valid) { int hdr = __float_as_int(S.rowS[r][RS_HDR]); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
+        if (valid) { int hdr = __float_as_int(ROWF(S, r, HDR)); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
 #pragma unroll
           for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L]; }
 #pragma unroll
@@ -989,7 +1068,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         for (int r0 = 0; r0 < m_total; r0 += 32) {
           const int r = r0 + lane; const bool valid = r < m_total;
           int lab = -1, fric = 0;
-          if (valid) { int hdr = __float_as_int(S.rowS[r][RS_HDR]); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
+          if (valid) { int hdr = __float_as_int(ROWF(S, r, HDR)); int g = body_group(hdr & 15); fric = ((hdr >> 8) & 255) != 255;
 #pragma unroll
             for (int L = 0; L < NISL; L++) if (g == L) lab = lab_of_group[L]; }
 #pragma unroll
@@ -1135,6 +1214,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
       __syncwarp();
       if (lane == 0) {
         Ctrl& c = S.c;
+        S.aux[5] = __int_as_float(0);
         c.ic_clock += (double)cfg.dt;
         if (c.ic_activated && c.ic_clock >= (double)c.ic_period) {
           const double delta_t = c.ic_clock;
@@ -1169,11 +1249,19 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
             }
             if (!cfg.exploration || !c.explore) {
               const float scaling[17] = {90, 45, 25, 25, 45, 100, 100, 100, 30, 30, 30, 100, 100, 100, 30, 30, 30};
-              float* in = P.policy_in + (size_t)env * 17;
-              for (int i = 0; i < 17; i++) in[i] = cur[i] / scaling[i];
-              int slot = atomicAdd(P.n_parked, 1);
-              P.parked_list[slot] = env;
-              park = true;
+              if (cfg.policy_precision == TFODE_POLICY_FP32) {
+                // fused actor: the environment's own warp runs TF_model::infer right here (actor_fused below), the two tanh
+                // outputs become the servo / boggie setpoints before this sub-step's control block -- no hand-off, no second launch
+                float* in = actor_scratch(S);
+                for (int i = 0; i < 17; i++) in[i] = cur[i] / scaling[i];
+                S.aux[5] = __int_as_float(1);
+              } else {
+                float* in = P.policy_in + (size_t)env * 17;
+                for (int i = 0; i < 17; i++) in[i] = cur[i] / scaling[i];
+                int slot = atomicAdd(P.n_parked, 1);
+                P.parked_list[slot] = env;
+                park = true;
+              }
             }
             for (int i = 0; i < 17; i++) c.last_state[i] = cur[i];
             c.has_last_state = 1;
@@ -1201,6 +1289,15 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         } else c.ic_tick = 0;
       }
       __syncwarp();
+      if (cfg.controller == TFODE_CTRL_MLP && __float_as_int(S.aux[5]) != 0) {   // warp-uniform: this environment's IC tick asks the actor
+        actor_fused(S, P.policy_w, lane);
+        if (lane == 0) {   // src/rover_1_tf.cc:184-185
+          const float* y = actor_scratch(S);
+          S.c.steering_rate = (double)y[0] * 15.0;
+          S.c.boggie_torque = (double)y[1] * 25.0;
+        }
+        __syncwarp();
+      }
 
       parked_now = S.c.parked == 1;  // hand the env to the policy kernel; part B runs in the next launch
     } else if (runnable) {
@@ -1309,7 +1406,11 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
   // ---------------------------------------------------------------- store the record
   __syncwarp();
   if (!valid) return;
-  if (lane == 0) P.budget[env] = budget;
+  if (lane == 0) {
+    P.budget[env] = budget;
+    if (S.cap_over) atomicAdd(P.cstats, (unsigned long long)S.cap_over);
+    if (S.cap_max > 0) atomicMax(P.cstats + 1, (unsigned long long)S.cap_max);
+  }
   {
     EnvRec* st = reinterpret_cast<EnvRec*>(&S.rowJ[0][0]);
     if (lane < NB) {
@@ -1389,6 +1490,26 @@ __global__ void observe_kernel(const EnvRec* rec, int n, float* obs17, float* re
   if (reward) reward[e] = (float)r.c.last_reward;
   if (done) done[e] = (uint8_t)(r.c.done_call != 0);
   if (ncont) ncont[e] = r.c.n_contacts;
+}
+// Rollout rows for the trainer (K7): what one policy tick hands back per environment, packed so that ONE collective moves it --
+// obs17 (Rover_1_tf::GetState), reward of the last IC tick, done flag of the last call, return and length of the last finished
+// episode (the `[Success] ... Rmoy` line of src/rover_training_1.cc:203-209), global environment id.
+__global__ void pack_rollout_kernel(const EnvRec* rec, int n, int env_id_offset, float* rows) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const EnvRec& r = rec[e];
+  float q[4] = {r.body[F_QUAT + 0][0], r.body[F_QUAT + 1][0], r.body[F_QUAT + 2][0], r.body[F_QUAT + 3][0]};
+  float R[9]; quatToR(R, q);
+  const float vx0 = R[0], vx1 = R[3], vx2 = R[6];
+  float direction = tfn::asin(vx1) * 57.29577951308232f;
+  if (vx0 < 0) direction = (vx1 > 0 ? 1.0f : -1.0f) * 180.0f - direction;
+  float* o = rows + (size_t)e * TFODE_ROLLOUT_WIDTH;
+  o[0] = direction; o[1] = r.c.jq_angle[1] * 57.29577951308232f; o[2] = tfn::asin(R[7]) * 57.29577951308232f;
+  o[3] = tfn::asin(-vx2) * 57.29577951308232f; o[4] = r.c.jq_angle[2] * 57.29577951308232f;
+  for (int i = 0; i < 12; i++) o[5 + i] = r.c.ft[i];
+  o[17] = (float)r.c.last_reward; o[18] = r.c.done_call != 0 ? 1.0f : 0.0f;
+  o[19] = r.c.last_ep_return; o[20] = (float)r.c.last_ep_steps; o[21] = (float)r.c.episodes_done;
+  o[22] = (float)(env_id_offset + e); o[23] = 0.0f;
 }
 __global__ void bodies_kernel(const EnvRec* rec, int n, float* out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;

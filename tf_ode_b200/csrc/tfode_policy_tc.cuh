@@ -294,15 +294,17 @@ inline int policy_tc_upload(PolicyTC& tcw, const float* w_host, cudaStream_t str
   return 0;
 }
 inline void policy_tc_free(PolicyTC& tcw) { cudaFree(tcw.w1c); cudaFree(tcw.w2c); tcw.w1c = tcw.w2c = nullptr; }
-inline int policy_tc_launch(PolicyTC& tcw, const float* in, const int* list, const int* n_list, int m_direct, int max_rows, const float* b1, const float* b2,
+// returns the CUDA status of the launch (cudaErrorInvalidValue when no weights were uploaded)
+inline cudaError_t policy_tc_launch(PolicyTC& tcw, const float* in, const int* list, const int* n_list, int m_direct, int max_rows, const float* b1, const float* b2,
                             const float* W3, const float* b3, EnvRec* rec, float* act_direct, cudaStream_t stream) {
-  if (!tcw.w1c || !tcw.w2c) return -1;
+  if (!tcw.w1c || !tcw.w2c) return cudaErrorInvalidValue;
   if (!tcw.attr_set) {
-    if (cudaFuncSetAttribute(policy_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES) != cudaSuccess) return -1;
+    const cudaError_t e = cudaFuncSetAttribute(policy_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES);
+    if (e != cudaSuccess) return e;
     tcw.attr_set = true;
   }
   const int blocks = (max_rows + TC_ROWS - 1) / TC_ROWS;
   policy_tc_kernel<<<blocks, TC_ROWS, TC_SMEM_BYTES, stream>>>(in, list, n_list, m_direct, tcw.w1c, tcw.w2c, b1, b2, W3, b3, rec, act_direct);
-  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+  return cudaGetLastError();
 }
 }  // namespace tfode

@@ -35,11 +35,23 @@ struct __align__(16) WarpSm {
                         // M^-1 J^T lambda accumulated by the sweeps (6 of 8 used)
   float cont[MAXC][8];  // pos, normal, depth, info bits (b1 | b2<<4 | soft<<8)
   float rowJ[MAXROWS][12];
+  // Row scalars.  Default layout: split by access pattern so that the sweeps' per-lane gathers (one row per lane, any row)
+  // spread over the banks -- {rhs, Ad, Ad*cfm, lo} as one 16-byte load (bank quad = row mod 8), {hi, lambda} as one 8-byte
+  // load (bank pair = row mod 16), header and c/entry words on their own.  The former 32-byte row record put every row's
+  // lambda on 4 of the 32 banks (8*row + 5) and the float4 on 4 of the 8 bank quads.  -DTFODE_ROWS_AOS restores it (A/B).
+#ifdef TFODE_ROWS_AOS
   float rowS[MAXROWS][8];  // rhs, Ad, Ad*cfm, lo, hi, lambda, hdr, (c during build)
+#else
+  float4 rowC[MAXROWS];    // rhs, Ad, Ad*cfm, lo
+  float2 rowHL[MAXROWS];   // hi, lambda
+  float rowHdr[MAXROWS];   // body1 | body2 << 4 | friction-normal row << 8 (bytes 0/1 later: the order arrays of reorders 1 and 2)
+  float rowCE[MAXROWS];    // c while the rows are built, then the row's two pre-decoded sweep-queue entries
+#endif
   unsigned char order[MAXROWS + 2];
   int isl_off[NISL + 1], isl_m[NISL + 1], isl_base[NISL + 1];
   int isl_lab[NISL + 1];  // island label of each base group (a group merged with a step box takes the smallest group index)
   int pgs_on, n_draws;
+  int cap_over, cap_max;   // contact-capacity audit of this launch: sub-steps over capacity, largest generated count
   float ftraw[12];
   float aux[12];
   Ctrl c;
@@ -48,6 +60,23 @@ struct __align__(16) WarpSm {
 static_assert(sizeof(EnvRec) <= sizeof(float) * MAXROWS * 12, "record staging aliases the row array");
 
 enum { RS_RHS = 0, RS_AD = 1, RS_ADCFM = 2, RS_LO = 3, RS_HI = 4, RS_LAM = 5, RS_HDR = 6, RS_C = 7, RS_ENT = 7 };
+// lvalue of scalar `f` (an RS_* name without the prefix) of row r
+#ifdef TFODE_ROWS_AOS
+#define ROWF(S, r, f) ((S).rowS[(r)][RS_##f])
+#define ROW_HDR_STRIDE 32
+#else
+#define ROWF_RHS(S, r) ((S).rowC[(r)].x)
+#define ROWF_AD(S, r) ((S).rowC[(r)].y)
+#define ROWF_ADCFM(S, r) ((S).rowC[(r)].z)
+#define ROWF_LO(S, r) ((S).rowC[(r)].w)
+#define ROWF_HI(S, r) ((S).rowHL[(r)].x)
+#define ROWF_LAM(S, r) ((S).rowHL[(r)].y)
+#define ROWF_HDR(S, r) ((S).rowHdr[(r)])
+#define ROWF_C(S, r) ((S).rowCE[(r)])
+#define ROWF_ENT(S, r) ((S).rowCE[(r)])
+#define ROWF(S, r, f) ROWF_##f(S, r)
+#define ROW_HDR_STRIDE 4
+#endif
 
 // ---------------------------------------------------------------- small math
 // fma placement of these products is fixed by the numerics contract (include/tfode_numerics.h); the kernels are

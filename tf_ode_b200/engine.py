@@ -19,8 +19,8 @@ _LIB = None
 EXPORTS = [
     "tfode_batch_config_default", "tfode_batch_create", "tfode_batch_destroy", "tfode_last_error",
     "tfode_batch_set_stream", "tfode_batch_reset", "tfode_batch_set_actions", "tfode_batch_set_speed",
-    "tfode_batch_load_policy", "tfode_batch_step", "tfode_batch_observe", "tfode_batch_get_bodies",
-    "tfode_batch_drain_transitions", "tfode_batch_rollout_host", "tfode_batch_get_state",
+    "tfode_batch_load_policy", "tfode_batch_step", "tfode_batch_observe", "tfode_batch_pack_rollout", "tfode_batch_get_bodies",
+    "tfode_batch_drain_transitions", "tfode_batch_contact_stats", "tfode_batch_rollout_host", "tfode_batch_get_state",
     "tfode_batch_set_state", "tfode_batch_launch_count", "tfode_batch_n_envs", "tfode_batch_sync",
     "tfode_policy_infer",
     "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
@@ -56,7 +56,9 @@ def load_library():
     L.tfode_batch_step.argtypes = [vp, i32]
     L.tfode_batch_observe.argtypes = [vp, vp, vp, vp, vp]
     L.tfode_batch_get_bodies.argtypes = [vp, vp]
-    L.tfode_batch_drain_transitions.argtypes = [vp, vp, i32, C.POINTER(i32)]
+    L.tfode_batch_pack_rollout.argtypes = [vp, vp]
+    L.tfode_batch_drain_transitions.argtypes = [vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]
+    L.tfode_batch_contact_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i32]
     L.tfode_batch_rollout_host.argtypes = [vp, vp, i32, vp, vp, vp]
     L.tfode_batch_get_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
     L.tfode_batch_set_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
@@ -226,13 +228,26 @@ class RoverBatch:
     def observe(self, obs=None, reward=None, done=None, ncontacts=None):
         self._ck(self.L.tfode_batch_observe(self.h, _dp(obs), _dp(reward), _dp(done), _dp(ncontacts)))
 
+    def pack_rollout(self, rows_dev):
+        """[n, abi.ROLLOUT_WIDTH] float32 device tensor: obs17 | reward | done | last episode return, steps | episodes | global id | 0."""
+        self._ck(self.L.tfode_batch_pack_rollout(self.h, _dp(rows_dev)))
+
     def get_bodies(self, out_dev):
         self._ck(self.L.tfode_batch_get_bodies(self.h, _dp(out_dev)))
 
     def drain_transitions(self, out_dev, max_rows):
-        n = C.c_int(0)
-        self._ck(self.L.tfode_batch_drain_transitions(self.h, _dp(out_dev), max_rows, C.byref(n)))
+        """Experience rows appended since the last drain -> out_dev[:n]; returns n (rows written).  `last_dropped` = rows lost to
+        the ring's transition_capacity since the previous drain.  Raises (nothing consumed) when the pending rows exceed max_rows."""
+        n, dropped = C.c_int(0), C.c_int(0)
+        self._ck(self.L.tfode_batch_drain_transitions(self.h, _dp(out_dev), max_rows, C.byref(n), C.byref(dropped)))
+        self.last_dropped = dropped.value
         return n.value
+
+    def contact_stats(self, reset=False):
+        """(environment sub-steps in which more contacts were generated than max_contacts keeps, largest generated count)."""
+        over, mx = C.c_int64(0), C.c_int64(0)
+        self._ck(self.L.tfode_batch_contact_stats(self.h, C.byref(over), C.byref(mx), int(reset)))
+        return over.value, mx.value
 
     def rollout_host(self, actions, n_substeps, obs, reward, done):
         """Host-buffer round trip (numpy arrays): H2D actions -> n steps -> D2H observations."""

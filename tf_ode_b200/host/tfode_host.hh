@@ -323,9 +323,10 @@ class Rover_1_tf : public Rover_1 {
     int cap = 4 * _env->n_envs(), n = 0;
     float* d = nullptr;
     if (cudaMalloc((void**)&d, (size_t)cap * TFODE_TRANSITION_WIDTH * sizeof(float)) != cudaSuccess) throw std::runtime_error("cudaMalloc failed");
-    int rc = tfode_batch_drain_transitions(b, d, cap, &n);
+    int dropped = 0;
+    int rc = tfode_batch_drain_transitions(b, d, cap, &n, &dropped);   // cap = the ring's default capacity, so pending rows always fit
     if (rc != TFODE_OK) { cudaFree(d); tfode_host::check(rc, b, "tfode_batch_drain_transitions"); }
-    if (n > cap) n = cap;
+    if (dropped) { cudaFree(d); throw std::runtime_error(std::to_string(dropped) + " experience tuples were lost: raise transition_capacity"); }
     std::vector<float> out((size_t)n * TFODE_TRANSITION_WIDTH);
     tfode_batch_sync(b);
     cudaMemcpy(out.data(), d, out.size() * sizeof(float), cudaMemcpyDeviceToHost);

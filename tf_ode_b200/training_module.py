@@ -51,7 +51,9 @@ def _run_episodes(actor_weights, n_episodes, exploration, seed, device, policy_p
                 break
         cap = cfg.transition_capacity
         buf = torch.zeros(cap, abi.TRANSITION_WIDTH, device="cuda")
-        n = min(batch.drain_transitions(buf, cap), cap)
+        n = batch.drain_transitions(buf, cap)
+        if batch.last_dropped:
+            raise RuntimeError("%d experience rows were lost: raise transition_capacity" % batch.last_dropped)
         rows = buf[:n].cpu().numpy()
         states = [batch.get_state(e) for e in range(n_episodes)]
     finally:

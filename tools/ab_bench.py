@@ -20,7 +20,7 @@ eng.LIB_PATH = sys.argv[1]
 import bench
 from tf_ode_b200 import RoverBatch, abi, glorot_policy
 wl, steps = sys.argv[2], int(sys.argv[3])
-n = bench.WORKLOADS[wl][1]
+n = bench.dev_envs(wl)
 g = RoverBatch(bench.make_cfg(wl, n), stream=torch.cuda.current_stream().cuda_stream)
 if g.cfg.controller == abi.CTRL_MLP:
     g.load_policy(glorot_policy())

@@ -48,7 +48,7 @@ def heightmaps():
         assert a.ndim == 3 and a.dtype == np.uint8
         out[k] = np.ascontiguousarray(a[..., 0])
         print("heightmap %s: %s levels %d..%d" % (k, out[k].shape, out[k].min(), out[k].max()))
-    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "heightmap_levels.npz"), **out)
+    np.savez_compressed(os.path.join(ROOT, "tf_ode_b200", "data", "heightmap_levels.npz"), **out)   # package data: the terrains of BASELINE configs 2 and 5
 
 
 def model_trees():

@@ -20,7 +20,7 @@ import bench  # noqa: E402
 from tf_ode_b200 import RoverBatch, abi, glorot_policy  # noqa: E402
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "config2"
-n = int(sys.argv[2]) if len(sys.argv) > 2 else bench.WORKLOADS[wl][1]
+n = int(sys.argv[2]) if len(sys.argv) > 2 else bench.dev_envs(wl)
 g = RoverBatch(bench.make_cfg(wl, n))
 if g.cfg.controller == abi.CTRL_MLP:
     g.load_policy(glorot_policy())
