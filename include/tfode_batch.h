@@ -254,6 +254,15 @@ int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, i
  * A non-zero first value means trajectories deviate from the reference's for that reason.  HOST pointers, either may be NULL. */
 int tfode_batch_contact_stats(TfodeBatch* b, int64_t* over_capacity_steps, int64_t* max_generated, int reset);
 
+/* The reference's debug print formats that scripts/bin/monitor-policies and the tree-fitting scripts read from stdout, built
+ * from one experience row (HOST float[TFODE_TRANSITION_WIDTH] as drained above):
+ *   TFODE_PRINT_TRANSITIONS        src/rover_1_tf.cc:125-136   "s0 .. s16 steer torque s'0 .. s'16\n"   (all "%f")
+ *   TFODE_PRINT_STATE_AND_ACTIONS  src/rover_1_tf.cc:190-195   "s0 .. s16 steer torque\n" -- the state of a tick and the action chosen
+ *                                  at it are the (state, action) of the tuple the NEXT tick appends, so the same rows serve.
+ * Writes a NUL-terminated line into out[cap]; returns its length, or TFODE_EINVAL (bad kind, cap too small: 1024 is enough). */
+enum { TFODE_PRINT_TRANSITIONS = 0, TFODE_PRINT_STATE_AND_ACTIONS = 1 };
+int tfode_format_transition(const float* row_host, int kind, char* out, size_t cap);
+
 /* Host-buffer round trip used by the end-to-end measurement: H2D actions (may be NULL),
  * n_substeps, D2H obs17/reward/done (HOST pointers, pinned or pageable; any may be NULL). */
 int tfode_batch_rollout_host(TfodeBatch* b, const float* actions_host, int n_substeps,

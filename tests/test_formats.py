@@ -423,3 +423,27 @@ def test_saved_model_errors_are_loud(tmp_path):
         f.truncate(1000)
     with pytest.raises(TfodeError, match="outside its data shard"):
         read_saved_model_actor(str(d))
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# PRINT_TRANSITIONS / PRINT_STATE_AND_ACTIONS row formats (src/rover_1_tf.cc:125-136,190-195), read by scripts/bin/monitor-policies
+# ----------------------------------------------------------------------------------------------------------------------
+def test_print_transitions_row_formats_match_the_reference_printf_calls():
+    from tf_ode_b200 import abi, format_transitions
+    rs = np.random.RandomState(4)
+    rows = np.zeros((5, abi.TRANSITION_WIDTH), np.float32)
+    rows[:, 0] = np.arange(5)
+    rows[:, 1:18] = rs.randn(5, 17) * 40
+    rows[:, 18:20] = rs.uniform(-1, 1, (5, 2)) * np.array([15, 25])
+    rows[:, 20] = rs.randn(5); rows[:, 21] = (0, 0, 1, 0, 1)
+    rows[:, 22:39] = rs.randn(5, 17) * 40
+    rows[2, 1] = -0.0000004; rows[3, 22] = 123456.789
+    # the reference: printf("%f ", s_i) x17, printf("%f %f", steer, torque), printf(" %f", s'_i) x17, printf("\n")
+    want = "".join("".join("%f " % float(v) for v in r[1:18]) + "%f %f" % (float(r[18]), float(r[19])) + "".join(" %f" % float(v) for v in r[22:39]) + "\n" for r in rows)
+    assert format_transitions(rows, 0) == want
+    # PRINT_STATE_AND_ACTIONS: printf("%f ", s_i) x17, printf("%f %f\n", steer, torque)
+    want = "".join("".join("%f " % float(v) for v in r[1:18]) + "%f %f\n" % (float(r[18]), float(r[19])) for r in rows)
+    assert format_transitions(rows, 1) == want
+    assert len(format_transitions(rows[:1], 0).split()) == 36 and len(format_transitions(rows[:1], 1).split()) == 19
+    with pytest.raises(Exception):
+        format_transitions(rows, 7)

@@ -722,6 +722,19 @@ int tfode_heightmap_load_png(const char* path, double z_scale, float** heights_o
   return tfode_heightmap_decode_png(buf.data(), buf.size(), z_scale, heights_out, nrow_out, ncol_out);
 }
 
+int tfode_format_transition(const float* row, int kind, char* out, size_t cap) {
+  if (!row || !out || cap == 0 || (kind != TFODE_PRINT_TRANSITIONS && kind != TFODE_PRINT_STATE_AND_ACTIONS)) return TFODE_EINVAL;
+  // src/rover_1_tf.cc:125-136 / :190-195: every value through "%f", blanks exactly where the reference's printf calls put them
+  size_t n = 0;
+  auto put = [&](const char* fmt, double v) { if (n < cap) { const int k = snprintf(out + n, cap - n, fmt, v); n += k > 0 ? (size_t)k : 0; } };
+  for (int i = 0; i < 17; i++) put("%f ", (double)row[1 + i]);
+  if (n < cap) { const int k = snprintf(out + n, cap - n, "%f %f", (double)row[18], (double)row[19]); n += k > 0 ? (size_t)k : 0; }
+  if (kind == TFODE_PRINT_TRANSITIONS) for (int i = 0; i < 17; i++) put(" %f", (double)row[22 + i]);
+  if (n + 1 >= cap) return TFODE_EINVAL;
+  out[n++] = '\n'; out[n] = 0;
+  return (int)n;
+}
+
 int tfode_savedmodel_read_actor(const char* saved_model_dir, float** weights_out, size_t* n_floats_out) {
   if (!saved_model_dir || !weights_out || !n_floats_out) { g_create_error = "null argument"; return TFODE_EINVAL; }
   *weights_out = nullptr; *n_floats_out = 0;

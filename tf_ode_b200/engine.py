@@ -25,7 +25,7 @@ EXPORTS = [
     "tfode_policy_infer",
     "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
     "tfode_heightmap_load_png", "tfode_heightmap_decode_png", "tfode_free",
-    "tfode_savedmodel_read_actor", "tfode_batch_load_policy_saved_model",
+    "tfode_savedmodel_read_actor", "tfode_batch_load_policy_saved_model", "tfode_format_transition",
 ]
 
 
@@ -76,6 +76,7 @@ def load_library():
     L.tfode_batch_load_policy_saved_model.argtypes = [vp, C.c_char_p]
     L.tfode_heightmap_load_png.argtypes = [C.c_char_p, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     L.tfode_heightmap_decode_png.argtypes = [C.c_char_p, C.c_size_t, C.c_double, C.POINTER(C.POINTER(C.c_float)), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    L.tfode_format_transition.argtypes = [vp, i32, C.c_char_p, C.c_size_t]
     L.tfode_free.argtypes = [vp]
     L.tfode_free.restype = None
     _LIB = L
@@ -132,6 +133,21 @@ def read_saved_model_actor(saved_model_dir):
         return np.ctypeslib.as_array(w, shape=(n.value,)).copy()
     finally:
         L.tfode_free(w)
+
+
+def format_transitions(rows, kind=0):
+    """PRINT_TRANSITIONS (kind 0, src/rover_1_tf.cc:125-136) / PRINT_STATE_AND_ACTIONS (kind 1, :190-195) text of experience rows
+    ([m, abi.TRANSITION_WIDTH] float32, as drained): one line per row, exactly what the reference's printf calls emit."""
+    L = load_library()
+    rows = np.ascontiguousarray(rows, dtype=np.float32).reshape(-1, abi.TRANSITION_WIDTH)
+    buf = C.create_string_buffer(1024)
+    out = []
+    for r in rows:
+        n = L.tfode_format_transition(r.ctypes.data_as(C.c_void_p), kind, buf, len(buf))
+        if n < 0:
+            raise TfodeError("tfode_format_transition failed (%d)" % n)
+        out.append(buf.raw[:n].decode())
+    return "".join(out)
 
 
 def _hp(a):

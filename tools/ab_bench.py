@@ -19,12 +19,15 @@ import tf_ode_b200.engine as eng
 eng.LIB_PATH = sys.argv[1]
 import bench
 from tf_ode_b200 import RoverBatch, abi, glorot_policy
-wl, steps = sys.argv[2], int(sys.argv[3])
+wl, steps, pre = sys.argv[2], int(sys.argv[3]), int(sys.argv[4])
 n = bench.dev_envs(wl)
-g = RoverBatch(bench.make_cfg(wl, n), stream=torch.cuda.current_stream().cuda_stream)
+cfg = bench.make_cfg(wl, n)
+if os.path.basename(sys.argv[1]).startswith("libr1"):
+    cfg.abi_version = 1   # the round-1 library: same config struct, older entry points
+g = RoverBatch(cfg, stream=torch.cuda.current_stream().cuda_stream)
 if g.cfg.controller == abi.CTRL_MLP:
     g.load_policy(glorot_policy())
-for _ in range(3):
+for _ in range(pre):
     g.step(100)
 torch.cuda.synchronize()
 a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -40,13 +43,14 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--workload", default="config2")
 ap.add_argument("--rounds", type=int, default=3)
 ap.add_argument("--steps", type=int, default=8)
+ap.add_argument("--pre", type=int, default=3, help="untimed 100-sub-step steps before the timed ones (40: wheels in the groove for config 2)")
 ap.add_argument("names", nargs="+")
 args = ap.parse_args()
 res = {n: [] for n in args.names}
 for r in range(args.rounds):
     for n in args.names:
         lib = os.path.join(ROOT, "build", "lib%s.so" % n)
-        out = subprocess.run([sys.executable, "-c", ONE, lib, args.workload, str(args.steps)], capture_output=True, text=True, timeout=600)
+        out = subprocess.run([sys.executable, "-c", ONE, lib, args.workload, str(args.steps), str(args.pre)], capture_output=True, text=True, timeout=600)
         if out.returncode != 0:
             print(n, "FAILED", out.stderr[-400:]); res[n].append(float("nan")); continue
         res[n].append(float(out.stdout.strip().splitlines()[-1]))
