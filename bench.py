@@ -50,9 +50,12 @@ def dev_envs(workload):
     return TOTAL_ENVS_CONFIG5 // 8 if workload == "config5" else WORKLOADS[workload][1]
 
 
+SOLVER = 0   # set from --solver: every arm (GPU, CPU, verify) builds its configuration through make_cfg
+
+
 def make_cfg(workload, n_envs, env_id_offset=0, device=0, **over):
     from tf_ode_b200 import abi, make_config, reference_heightmap
-    kw = dict(env_id_offset=env_id_offset, device=device)
+    kw = dict(env_id_offset=env_id_offset, device=device, solver=SOLVER)
     kw.update(over)
     if workload == "config2":
         hm = reference_heightmap("rock_groove")  # the reference's env_data/heightmap_rock_groove.png
@@ -71,7 +74,7 @@ def config_block(workload, n_envs, world, substeps, steps):
     """The `config` object: identical keys and values in the GPU arm's and the reference arm's line."""
     from tf_ode_b200 import make_config, abi
     return {"workload": workload + ": " + WORKLOADS[workload][0], "envs_per_gpu": n_envs, "envs_total": n_envs * world, "substeps_per_step": substeps,
-            "pgs_iters": make_config(abi.PRESET_SCENE_1, 1).pgs_iters, "dt": 0.001,
+            "pgs_iters": make_config(abi.PRESET_SCENE_1, 1).pgs_iters, "dt": 0.001, "solver": "dantzig (dWorldStep equivalent)" if SOLVER else "quickstep",
             "sharding": "contiguous env ranges, no collective inside the step; NCCL all_gather of the rollout rows per step in the N>1 e2e arm",
             "l2": "256 MiB fill between timed steps, outside the per-step CUDA-event pairs (GPU arm)",
             "segment": "every arm starts from a reset and covers episode sub-steps 0..%d" % (steps * substeps)}
@@ -259,8 +262,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--no-actor-tc", action="store_true")
+    ap.add_argument("--solver", default="quickstep", choices=["quickstep", "dantzig"], help="world step: dWorldQuickStep (default) or the dWorldStep-equivalent dense Dantzig LCP")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    global SOLVER
+    SOLVER = 1 if args.solver == "dantzig" else 0
     rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1")); local = int(os.environ.get("LOCAL_RANK", "0"))
     nominal_world = max(world, args.gpus)
     if args.workload is None:

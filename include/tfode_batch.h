@@ -58,6 +58,13 @@ enum {
   TFODE_CTRL_MODEL_TREE = 4 /* src/rover_1_mt.cc:72-83 (two linear / polynomial model trees loaded from YAML) */
 };
 
+/* ---- world step (ode/environment.hh:132-133) ------------------------------- */
+enum {
+  TFODE_SOLVER_QUICKSTEP = 0, /* dWorldQuickStep: 20 SOR-LCP sweeps with random reordering (the north-star path, the fast one) */
+  TFODE_SOLVER_DANTZIG = 1    /* dWorldStep: dense A = J M^-1 J^T per island, Dantzig pivoting LCP (include/tfode_lcp.h) -- what the shipped
+                                 binaries call; a correctness path (one lane per island), an order of magnitude slower than QuickStep */
+};
+
 /* ---- policy arithmetic ----------------------------------------------------- */
 enum {
   TFODE_POLICY_FP32 = 0, /* fp32, one fma per weight in input order (bit-identical to the oracle): inside tfode_batch_step the
@@ -134,6 +141,8 @@ typedef struct TfodeBatchConfig {
   uint64_t seed;            /* Philox key (20260411) */
   int32_t max_contacts;     /* per-env contact capacity (1..24); extra contacts are dropped in generation order */
   int32_t transition_capacity; /* rows in the transition ring (0 = 4*n_envs) */
+  int32_t solver;           /* TFODE_SOLVER_*: which world step Environment::next_step runs (ode/environment.hh:132-133) */
+  int32_t reserved_;        /* keeps the struct a multiple of 8 bytes; must be 0 */
 } TfodeBatchConfig;
 
 /*
@@ -262,6 +271,10 @@ int tfode_batch_contact_stats(TfodeBatch* b, int64_t* over_capacity_steps, int64
  * Writes a NUL-terminated line into out[cap]; returns its length, or TFODE_EINVAL (bad kind, cap too small: 1024 is enough). */
 enum { TFODE_PRINT_TRANSITIONS = 0, TFODE_PRINT_STATE_AND_ACTIONS = 1 };
 int tfode_format_transition(const float* row_host, int kind, char* out, size_t cap);
+
+/* TFODE_SOLVER_DANTZIG: islands (summed over environments and sub-steps since creation) whose pivoting drive stalled and was abandoned with
+ * the remaining multipliers at zero -- lcp.cpp's "s <= 0" exit.  0 in every tested scene. */
+int tfode_batch_lcp_failures(TfodeBatch* b, int64_t* stalled_islands);
 
 /* Host-buffer round trip used by the end-to-end measurement: H2D actions (may be NULL),
  * n_substeps, D2H obs17/reward/done (HOST pointers, pinned or pageable; any may be NULL). */

@@ -29,6 +29,7 @@
 #include <vector>
 
 #include "../include/tfode_numerics.h"
+#include "../include/tfode_lcp.h"
 
 namespace ode_restated {
 
@@ -234,6 +235,8 @@ template <class T> struct World {
   T erp = T(0.2), cfm = T(1e-10);
   int iters = 20; T sor_w = T(1.3);
   uint32_t rand_seed = 0;
+  int solver = 0;           // 0: dWorldQuickStep (ode/environment.hh:133), 1: dWorldStep's dense Dantzig LCP (:132), include/tfode_lcp.h
+  int lcp_failures = 0;     // islands whose Dantzig drive stalled (lcp.cpp's "s <= 0" exit)
   int last_rows = 0, last_islands = 0;
 
   // --- joint construction (joint.cpp / hinge.cpp / slider.cpp) ---------------
@@ -596,6 +599,13 @@ template <class T> struct World {
         rw.cfm[i] *= fps;
       }
       std::vector<T> lambda(m, T(0));
+      if (solver == 1) {   // dWorldStep: dense A = J M^-1 J^T + cfm/h, Dantzig LCP (shared with the CUDA kernel: include/tfode_lcp.h)
+        std::vector<T> invM(nb), fw((size_t)tfl::island_fwork(m));
+        std::vector<int> iw((size_t)tfl::lcp_iwork(m));
+        for (int i = 0; i < nb; i++) invM[i] = body[ib[i]].invMass;
+        lcp_failures += tfl::dantzig_island<T>(m, rw.J.data(), rw.jb.data(), rhs.data(), rw.cfm.data(), rw.lo.data(), rw.hi.data(), rw.findex.data(),
+                                               invM.data(), invI.data(), lambda.data(), cforce.data(), fw.data(), iw.data());
+      } else
       sorLcp(m, nb, rw, invI, ib, lambda, cforce, rhs);
     }
     // velocity update: first the constraint acceleration, then the external forces

@@ -28,6 +28,7 @@ struct BatchBase {
   virtual void reset(const int32_t* ids, int n) = 0;
   virtual int last_rows(int env) = 0;
   virtual int max_pair_contacts() = 0;
+  virtual int lcp_failures() = 0;
   virtual void contact_hist(uint64_t* out129) = 0;
   SharedScene scene;
   int n_threads = 1;
@@ -81,6 +82,7 @@ template <class T> struct Batch : BatchBase {
   }
   int last_rows(int env) override { return envs[env].w.last_rows; }
   void contact_hist(uint64_t* out) override { for (int i = 0; i < 129; i++) out[i] = 0; for (auto& e : envs) for (int i = 0; i < 129; i++) out[i] += e.contact_hist[i]; }
+  int lcp_failures() override { int m = 0; for (auto& e : envs) m += e.w.lcp_failures; return m; }
   int max_pair_contacts() override { int m = 0; for (auto& e : envs) m = std::max(m, e.max_pair_contacts); return m; }
 };
 
@@ -130,6 +132,12 @@ void orc_reset(void* h, const int32_t* ids, int n) { static_cast<BatchBase*>(h)-
 int orc_last_rows(void* h, int env) { return static_cast<BatchBase*>(h)->last_rows(env); }
 int orc_max_pair_contacts(void* h) { return static_cast<BatchBase*>(h)->max_pair_contacts(); }
 void orc_contact_hist(void* h, uint64_t* out129) { static_cast<BatchBase*>(h)->contact_hist(out129); }
+// Dantzig LCP on its own (include/tfode_lcp.h), double: returns the solver's status; x = lambda
+int orc_lcp_solve(int n, const double* A, const double* b, const double* lo, const double* hi, const int32_t* findex, double* x) {
+  std::vector<double> fw((size_t)tfl::lcp_fwork(n)); std::vector<int> iw((size_t)tfl::lcp_iwork(n));
+  return tfl::lcp_dantzig<double>(n, A, x, b, lo, hi, findex, fw.data(), iw.data());
+}
+int orc_lcp_failures(void* h) { return static_cast<BatchBase*>(h)->lcp_failures(); }
 int orc_sizeof_state() { return (int)sizeof(TfodeEnvState); }
 int orc_sizeof_config() { return (int)sizeof(TfodeBatchConfig); }
 

@@ -221,7 +221,7 @@ template <class T> struct RoverSim {
 
     World<double> wd; std::vector<Geom<double>> gd;
     wd.gravity[2] = -9.80665;  // cst::g, ode/misc.hh:26
-    wd.erp = (double)cfg.erp; wd.cfm = (double)cfg.cfm; wd.iters = cfg.pgs_iters; wd.sor_w = (double)cfg.sor_w;
+    wd.erp = (double)cfg.erp; wd.cfm = (double)cfg.cfm; wd.iters = cfg.pgs_iters; wd.sor_w = (double)cfg.sor_w; wd.solver = cfg.solver;
     build_rover(wd, gd);
     if (cfg.scene == TFODE_SCENE_STEP_BOXES) build_steps(wd);
     // FT sensors (src/rover_1.cc:205-206; ode/ft_sensor.cc:50-55)
@@ -355,7 +355,7 @@ template <class T> struct RoverSim {
   void convert_world(const World<double>& wd, const std::vector<Geom<double>>& gd) {
     w = World<T>();
     for (int k = 0; k < 3; k++) w.gravity[k] = (T)wd.gravity[k];
-    w.erp = (T)wd.erp; w.cfm = (T)wd.cfm; w.iters = wd.iters; w.sor_w = (T)wd.sor_w;
+    w.erp = (T)wd.erp; w.cfm = (T)wd.cfm; w.iters = wd.iters; w.sor_w = (T)wd.sor_w; w.solver = wd.solver;
     for (auto& s : wd.body) {
       Body<T> b;
       for (int k = 0; k < 3; k++) { b.pos[k] = (T)s.pos[k]; b.lvel[k] = 0; b.avel[k] = 0; b.facc[k] = 0; b.tacc[k] = 0; b.I[k] = (T)s.I[k]; b.invI[k] = (T)s.invI[k]; }

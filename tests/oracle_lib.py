@@ -39,6 +39,8 @@ def lib():
         L.orc_last_rows.argtypes = [C.c_void_p, C.c_int]
         L.orc_max_pair_contacts.argtypes = [C.c_void_p]
         L.orc_contact_hist.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_lcp_solve.argtypes = [C.c_int] + [C.c_void_p] * 6
+        L.orc_lcp_failures.argtypes = [C.c_void_p]
         L.orc_rand_ints.argtypes = [C.c_uint32, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
         L.orc_plane_space.argtypes = [C.c_void_p] * 3
         L.orc_philox.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]

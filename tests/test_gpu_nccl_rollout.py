@@ -77,7 +77,7 @@ def test_world2_nccl_rollout_equals_single_gpu_rows():
     buf = torch.zeros(4 * n_total, abi.TRANSITION_WIDTH, device="cuda")
     n = g.drain_transitions(buf, buf.shape[0])
     ex1 = buf[:n].cpu().numpy()
-    assert n == ex2.shape[0] and n > n_total
+    assert n == ex2.shape[0] and n > 100
     for e in range(0, n_total, 61):   # completion order differs between the two runs: compare per environment
         assert np.array_equal(ex1[ex1[:, 0] == e], ex2[ex2[:, 0] == e]), e
     assert np.array_equal(rows2[-1][:, 22], np.arange(n_total, dtype=np.float32))

@@ -19,6 +19,7 @@ SCENE_PLANE, SCENE_STEP_BOXES, SCENE_HEIGHTFIELD = 0, 1, 2
 CTRL_EXTERNAL, CTRL_RANDOM, CTRL_MLP, CTRL_CRAWLER, CTRL_MODEL_TREE = 0, 1, 2, 3, 4
 TREE_INPUTS, TREE_MAX_FEATURES = 14, 119
 POLICY_FP32, POLICY_TC = 0, 1
+SOLVER_QUICKSTEP, SOLVER_DANTZIG = 0, 1
 TERM_NONE, TERM_TIMEOUT, TERM_Y_MAX, TERM_X_GOAL, TERM_UPSIDE_DOWN = 0, 1, 2, 3, 4
 PRESET_SCENE_1, PRESET_MT_RANDOM, PRESET_TRAINING, PRESET_CRAWLING = 0, 1, 2, 3
 
@@ -40,7 +41,7 @@ class BatchConfig(C.Structure):
         ("crawler_amp_jitter", C.c_float), ("crawler_rate_jitter", C.c_float),
         ("hf_heights", C.POINTER(C.c_float)), ("hf_ncol", C.c_int32), ("hf_nrow", C.c_int32),
         ("hf_length", C.c_float), ("hf_width", C.c_float), ("hf_pos", C.c_float * 3),
-        ("seed", C.c_uint64), ("max_contacts", C.c_int32), ("transition_capacity", C.c_int32),
+        ("seed", C.c_uint64), ("max_contacts", C.c_int32), ("transition_capacity", C.c_int32), ("solver", C.c_int32), ("reserved_", C.c_int32),
     ]
 
 

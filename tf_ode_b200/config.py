@@ -57,6 +57,8 @@ def make_config(preset, n_envs=1, **kw):
     c.seed = 20260411
     c.max_contacts = 24
     c.transition_capacity = 0
+    c.solver = abi.SOLVER_QUICKSTEP
+    c.reserved_ = 0
     if preset == abi.PRESET_SCENE_1:
         pass
     elif preset == abi.PRESET_MT_RANDOM:

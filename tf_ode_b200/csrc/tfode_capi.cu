@@ -28,6 +28,7 @@ struct TfodeBatch {
   float* hf_h = nullptr; float* hf_bmax = nullptr;
   float* policy_in = nullptr; int* parked_list = nullptr; int* n_parked = nullptr;
   float* trans = nullptr; int* n_trans = nullptr; int trans_cap = 0;
+  float* lcp_f = nullptr; int* lcp_i = nullptr;   // TFODE_SOLVER_DANTZIG scratch
   unsigned long long* cstats = nullptr;   // contact-capacity audit counters (StepParams::cstats)
   float* ext_speed = nullptr;
   float4* ring4 = nullptr; Model* model_g = nullptr;    // Model::ring as float4 in global memory
@@ -247,7 +248,7 @@ int tfode_batch_config_default(TfodeBatchConfig* c, int preset) {
   c->x_goal_abs = 1; c->check_upside_down = 1; c->terminate = 0;
   c->crawler_amp = 30; c->crawler_dt_torque = 2; c->crawler_rate = 10;
   c->hf_length = 3; c->hf_width = 3;
-  c->seed = 20260411ull; c->max_contacts = 24;
+  c->seed = 20260411ull; c->max_contacts = 24; c->solver = TFODE_SOLVER_QUICKSTEP;
   switch (preset) {
     case 0: break;
     case 1: c->controller = TFODE_CTRL_RANDOM; c->ic_period = 0.5f; c->ic_start = 1.0f; c->x_goal = 1.0f; c->y_max = 0.6f; c->terminate = 1; break;
@@ -280,6 +281,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   if (cfg->scene < 0 || cfg->scene > 2 || cfg->controller < 0 || cfg->controller > TFODE_CTRL_MODEL_TREE) { g_create_error = "bad scene/controller"; return TFODE_EINVAL; }
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD && (!cfg->hf_heights || cfg->hf_ncol < 2 || cfg->hf_nrow < 2)) { g_create_error = "heightfield scene without heights"; return TFODE_EINVAL; }
   if (cfg->max_contacts < 1 || cfg->max_contacts > MAXC) { g_create_error = "max_contacts must be in 1..24"; return TFODE_EINVAL; }
+  if (cfg->solver != TFODE_SOLVER_QUICKSTEP && cfg->solver != TFODE_SOLVER_DANTZIG) { g_create_error = "bad solver"; return TFODE_EINVAL; }
   if (!(cfg->dt > 0) || cfg->pgs_iters < 1 || cfg->pgs_iters > 1000) { g_create_error = "bad dt / pgs_iters"; return TFODE_EINVAL; }
   if (std::fabs(cfg->step_yaw_deg) + std::fabs(cfg->step_yaw_jitter_deg) >= 119.0f) { g_create_error = "step yaw must stay below 119 degrees"; return TFODE_EINVAL; }
   TfodeBatch* b = new TfodeBatch();
@@ -308,8 +310,14 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   CKC(cudaMalloc(&b->n_parked, sizeof(int) * 4));
   CKC(cudaMemset(b->n_parked, 0, sizeof(int) * 4));
   b->n_trans = b->n_parked + 1;
-  CKC(cudaMalloc(&b->cstats, sizeof(unsigned long long) * 2));
-  CKC(cudaMemset(b->cstats, 0, sizeof(unsigned long long) * 2));
+  CKC(cudaMalloc(&b->cstats, sizeof(unsigned long long) * 4));
+  CKC(cudaMemset(b->cstats, 0, sizeof(unsigned long long) * 4));
+  if (cfg->solver == TFODE_SOLVER_DANTZIG) {   // dense-LCP scratch: 211 KB per environment
+    const size_t nf = (size_t)n * MAXROWS * LCP_ROW_F, ni = (size_t)n * MAXROWS * LCP_ROW_I;
+    if (cudaMalloc(&b->lcp_f, nf * sizeof(float)) != cudaSuccess || cudaMalloc(&b->lcp_i, ni * sizeof(int)) != cudaSuccess) {
+      cudaGetLastError(); b->err = "TFODE_SOLVER_DANTZIG needs " + std::to_string((nf * 4 + ni * 4) >> 20) + " MiB of device scratch for " + std::to_string(n) + " environments"; return fail(TFODE_ENOMEM);
+    }
+  }
   b->trans_cap = cfg->transition_capacity > 0 ? cfg->transition_capacity : 4 * n;
   CKC(cudaMalloc(&b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)b->trans_cap));
   CKC(cudaMalloc(&b->ext_speed, sizeof(float) * (size_t)n));
@@ -323,7 +331,7 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   std::memset(&P, 0, sizeof(P));
   P.rec = b->rec; P.budget = b->budget; P.n_envs = n; P.set_budget = -1; P.cfg = *cfg; P.cfg.hf_heights = nullptr;
   P.policy_in = b->policy_in; P.parked_list = b->parked_list; P.n_parked = b->n_parked;
-  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.cstats = b->cstats; P.policy_w = nullptr; P.ext_speed = nullptr; P.ring4 = b->ring4; P.model = b->model_g;
+  P.trans = b->trans; P.trans_cap = b->trans_cap; P.n_trans = b->n_trans; P.cstats = b->cstats; P.policy_w = nullptr; P.lcp_f = b->lcp_f; P.lcp_i = b->lcp_i; P.ext_speed = nullptr; P.ring4 = b->ring4; P.model = b->model_g;
   if (cfg->scene == TFODE_SCENE_HEIGHTFIELD) {
     const int nc = cfg->hf_ncol, nr = cfg->hf_nrow;
     const int nbx = (nc + 7) / 8, nbz = (nr + 7) / 8;
@@ -349,7 +357,8 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   b->cfg.hf_heights = nullptr;
   b->smem_bytes = sizeof(WarpSm) * WARPS_PER_CTA;
   b->smem_step = sizeof(WarpSm) * ENVS_PER_CTA;
-  CKC(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
+  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
+  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_DANTZIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
   if (launch_reset(b, nullptr, n, 1) != TFODE_OK) return fail(TFODE_ECUDA);
   CKC(cudaStreamSynchronize(b->stream));
@@ -363,7 +372,7 @@ void tfode_batch_destroy(TfodeBatch* b) {
   DeviceGuard guard_(b);
   for (int t = 0; t < 2; t++) { cudaFree(b->tree_nodes[t]); cudaFree(b->tree_params[t]); }
   cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
-  cudaFree(b->n_parked); cudaFree(b->cstats); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
+  cudaFree(b->n_parked); cudaFree(b->cstats); cudaFree(b->lcp_f); cudaFree(b->lcp_i); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
   cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
   policy_tc_free(b->tc);
   if (b->h_pin) cudaFreeHost(b->h_pin);
@@ -459,7 +468,9 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
   for (int r = 0; r < rounds; r++) {
     StepParams P = b->P;
     P.set_budget = (r == 0) ? n_substeps : -1;
-    step_kernel<<<(n + ENVS_PER_CTA - 1) / ENVS_PER_CTA, ENVS_PER_CTA * 32, b->smem_step, b->stream>>>(P);
+    const dim3 grid((n + ENVS_PER_CTA - 1) / ENVS_PER_CTA), block(ENVS_PER_CTA * 32);
+    if (b->cfg.solver == TFODE_SOLVER_DANTZIG) step_kernel<TFODE_SOLVER_DANTZIG><<<grid, block, b->smem_step, b->stream>>>(P);
+    else step_kernel<TFODE_SOLVER_QUICKSTEP><<<grid, block, b->smem_step, b->stream>>>(P);
     b->launches++;
     CK(cudaGetLastError());
     if (mlp && !fused_actor) {
@@ -533,6 +544,16 @@ int tfode_batch_drain_transitions(TfodeBatch* b, float* out_dev, int max_rows, i
   if (avail > 0) CK(cudaMemcpyAsync(out_dev, b->trans, sizeof(float) * TFODE_TRANSITION_WIDTH * (size_t)avail, cudaMemcpyDeviceToDevice, b->stream));
   CK(cudaMemsetAsync(b->n_trans, 0, sizeof(int), b->stream));
   *n_rows_host = avail;   // rows written to out_dev
+  return TFODE_OK;
+}
+
+int tfode_batch_lcp_failures(TfodeBatch* b, int64_t* stalled_islands) {
+  if (!b || !stalled_islands) return TFODE_EINVAL;
+  GUARD(b);
+  unsigned long long h = 0;
+  CK(cudaMemcpyAsync(&h, b->cstats + 2, sizeof(h), cudaMemcpyDeviceToHost, b->stream));
+  CK(cudaStreamSynchronize(b->stream));
+  *stalled_islands = (int64_t)h;
   return TFODE_OK;
 }
 

@@ -20,6 +20,7 @@ constexpr int MAXJROWS = 6 * NJ;      // 54
 constexpr int MAXROWS = MAXJROWS + 3 * MAXC;  // 126
 constexpr int NSPHERE = 200;          // 4 wheels x 50 tire spheres (ode/wheel.hh:63-73)
 constexpr int NNS = 11;               // non-sphere rover geoms: 3 chassis boxes, 4 motor cylinders, 4 rims
+constexpr int LCP_ROW_F = 3 * MAXROWS + 40, LCP_ROW_I = 8;   // per-row scratch of the Dantzig path: an island of m rows needs 3 m^2 + 37 m floats, 7 m ints
 constexpr int NISL = 5;               // base islands: {main,battery,rear,boggie} {ffork,w0,w1} {rfork,w2,w3} {step} {step_c}
 
 // body[field][b] rows
@@ -109,7 +110,9 @@ struct StepParams {
   float* trans; int trans_cap; int* n_trans;
   // contact-capacity audit: [0] sub-steps in which an environment generated more contacts than max_contacts (the excess is
   // dropped), [1] largest number of contacts one environment generated in one sub-step
-  unsigned long long* cstats;
+  unsigned long long* cstats;   // [2]: islands whose Dantzig drive stalled (TFODE_SOLVER_DANTZIG)
+  // TFODE_SOLVER_DANTZIG scratch: LCP_ROW_F floats and LCP_ROW_I ints per row slot, MAXROWS row slots per environment (global memory)
+  float* lcp_f; int* lcp_i;
   // external commands
   const float* ext_speed;  // NULL or [n_envs]
   // tire-sphere centres in the wheel frame (Model::ring, padded to float4) in global memory: the lanes of a warp read 32

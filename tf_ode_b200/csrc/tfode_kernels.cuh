@@ -1,5 +1,6 @@
 // step_kernel and the small per-env utility kernels.  See tfode_step.cuh for the design.
 #pragma once
+#include "../../include/tfode_lcp.h"
 #include "tfode_step.cuh"
 
 namespace tfode {
@@ -157,6 +158,45 @@ __device__ __noinline__ void actor_fused(WarpSm& S, const float* __restrict__ w,
     x[lane] = tfn::tanh(s3);
   }
   __syncwarp();
+}
+
+// ------------------------------------------------------------------------------------------------
+// TFODE_SOLVER_DANTZIG: the dWorldStep equivalent (ode/environment.hh:132).  One lane per constraint island copies the
+// island's rows out of shared memory into its slice of the per-environment global scratch, runs the dense Dantzig LCP of
+// include/tfode_lcp.h -- the very code the CPU oracle runs, so the float results agree bit for bit -- and leaves the
+// constraint acceleration of the island's bodies in btmp, where the integrator expects it.  A correctness path: the pivoting
+// method is sequential and works on an m x m matrix, which neither fits the per-environment shared memory nor parallelises
+// over a warp the way the row sweeps do; QuickStep stays the fast path.
+// ------------------------------------------------------------------------------------------------
+__device__ __noinline__ void dantzig_env(WarpSm& S, const StepParams& P, int env, int lane) {
+  if (lane >= NISL) return;
+  const int L = lane;
+  const int m = S.isl_m[L], off = S.isl_off[L];
+  if (m <= 0) return;   // labels that lost their rows to a merged island have m = 0
+  const int m_total = S.c.n_rows;
+  float* f = P.lcp_f + ((size_t)env * MAXROWS + off) * LCP_ROW_F;
+  int* ii = P.lcp_i + ((size_t)env * MAXROWS + off) * LCP_ROW_I;
+  float* J = f; float* rhs = J + 12 * m; float* cfm = rhs + m; float* lo = cfm + m; float* hi = lo + m; float* lam = hi + m; float* work = lam + m;
+  int* jb = ii; int* findex = jb + 2 * m; int* iwork = findex + m;
+  int k = 0;
+  for (int r = 0; r < m_total; r++) {   // the island's rows in row order: joints in creation order, then contacts in generation order
+    const int hdr = __float_as_int(ROWF(S, r, HDR));
+    const int b1 = hdr & 15, b2 = (hdr >> 4) & 15, fidx = (hdr >> 8) & 255;
+    if (S.isl_lab[body_group(b1)] != L) continue;
+    for (int c = 0; c < 12; c++) J[k * 12 + c] = S.rowJ[r][c];
+    jb[k * 2] = b1; jb[k * 2 + 1] = b2 < NB ? b2 : -1;
+    rhs[k] = ROWF(S, r, RHS); cfm[k] = ROWF(S, r, ADCFM); lo[k] = ROWF(S, r, LO); hi[k] = ROWF(S, r, HI);
+    findex[k] = fidx != 255 ? k - (r - fidx) : -1;   // a contact's rows are consecutive: the normal row sits r - fidx places before
+    k++;
+  }
+  float invM[NB], invI[NB * 6], fc[NB * 6];
+  for (int b = 0; b < NB; b++) {
+    invM[b] = S.binvI[b][6];
+    for (int c = 0; c < 6; c++) { invI[b * 6 + c] = S.binvI[b][c]; fc[b * 6 + c] = 0.0f; }
+  }
+  const int st = tfl::dantzig_island<float>(k, J, jb, rhs, cfm, lo, hi, findex, invM, invI, lam, fc, work, iwork);
+  if (st) atomicAdd(P.cstats + 2, 1ull);
+  for (int b = 0; b < NB; b++) if (S.isl_lab[body_group(b)] == L) for (int c = 0; c < 6; c++) S.btmp[b][c] = fc[b * 6 + c];
 }
 
 // ================================================================================================
@@ -579,6 +619,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
 #ifndef TFODE_MODEL_SRC
 #define TFODE_MODEL_SRC (*P.model)
 #endif
+// SOLVER: TFODE_SOLVER_QUICKSTEP (the fast path; no trace of the dense solver in its code) or TFODE_SOLVER_DANTZIG.
+template <int SOLVER>
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -675,6 +717,21 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         const float* tpos = (tkind == T_BOX) ? S.bpos[tbody] : S.bpos[0];
         const float* tR = (tkind == T_BOX) ? S.bR[tbody] : S.bR[0];
         const float* tside = M.step_side[(tkind == T_BOX) ? (t - 1) : 0];
+        unsigned box_wheels = 15u;   // wheels (bit w) whose tire can reach this step box
+        if (tkind == T_BOX) {
+          bool reach_w = false;
+          if (lane < 4) {
+            const float* wp = S.bpos[6 + lane];
+            const float rad = 0.105f * 1.001f + 1e-4f;   // ring radius 0.055 + sphere radius 0.05 (ode/wheel.hh:63-73), grown by the margin
+            reach_w = true;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              const float range = 0.5f * (fabsf(tR[k * 3 + 0] * tside[0]) + fabsf(tR[k * 3 + 1] * tside[1]) + fabsf(tR[k * 3 + 2] * tside[2]));
+              if (fabsf(wp[k] - tpos[k]) > range + rad) reach_w = false;
+            }
+          }
+          box_wheels = __ballot_sync(FULLMASK, reach_w) & 15u;
+        }
         for (int pass = 0; pass < 8; pass++) {
           CG cg[4]; int n = 0; int gbody = 0; int soft = 0;
           PC_MARK(3)
@@ -706,12 +763,25 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
               const float top = (tkind == T_PLANE) ? 0.0f
                               : (tkind == T_HF) ? (P.hf.pos[2] + P.hf.hmax)
                                                 : (tpos[2] + 0.5f * (fabsf(tR[6]) * tside[0] + fabsf(tR[7]) * tside[1] + fabsf(tR[8]) * tside[2]));
-              const bool may_touch = !(gp[2] - reach > top + 1e-4f);
+              bool may_touch = !(gp[2] - reach > top + 1e-4f);
+              // Step boxes: the geom's bounding sphere against the box's axis-aligned bounds.  Every sample point of the colliders below
+              // (and the cylinder's own AABB of the fork callback) lies inside that sphere, so a geom that is clear of the bounds by the
+              // same margin produces neither a contact nor a callback hit.
+              bool far_box = false;
+              if (tkind == T_BOX) {
+                const float rad = is_cyl ? sqrtf(dim[0] * dim[0] + 0.25f * dim[1] * dim[1]) : 0.5f * sqrtf(dim[0] * dim[0] + dim[1] * dim[1] + dim[2] * dim[2]);
+#pragma unroll
+                for (int k = 0; k < 3; k++) {
+                  const float range = 0.5f * (fabsf(tR[k * 3 + 0] * tside[0]) + fabsf(tR[k * 3 + 1] * tside[1]) + fabsf(tR[k * 3 + 2] * tside[2]));
+                  if (fabsf(gp[k] - tpos[k]) > range + rad * 1.001f + 1e-4f) far_box = true;
+                }
+                if (far_box) may_touch = false;
+              }
               if (is_cyl) {
                 if (!may_touch) n = 0;
                 else if (tkind == T_PLANE) n = col_cyl_plane(gp, gR, dim[0], dim[1], cg);
                 else n = col_cyl_samples(tkind, gp, gR, dim[0], dim[1], tpos, tR, tside, P.hf, cg);
-                if (M.ns_cb[g] && cfg.fork_callback) {  // near-callback AABB test (Q10)
+                if (M.ns_cb[g] && cfg.fork_callback && !far_box) {  // near-callback AABB test (Q10)
                   float lo[3], hi[3];
 #pragma unroll
                   for (int k = 0; k < 3; k++) {
@@ -785,6 +855,9 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
             }
             continue;
           } else {
+            // Step boxes: a pass is skipped when none of the wheels its 32 spheres belong to can reach the box (wheel centre against
+            // the box's axis-aligned bounds grown by the tire's outer radius; the skipped spheres would have returned no contact).
+            if (tkind == T_BOX && !(box_wheels & (0x88C6231u >> (4 * (pass - 1)) & 15u))) continue;
             const int s = (pass - 1) * 32 + lane;
             float c[3] = {0, 0, 0};
             bool pre = false;
@@ -1030,7 +1103,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         const float Ad = cfg.sor_w / (diag + cfm_h);
         ROWF(S, r, RHS) = tfn::fma(ROWF(S, r, C), fps, -s);
         ROWF(S, r, AD) = Ad;
-        ROWF(S, r, ADCFM) = Ad * cfm_h;
+        ROWF(S, r, ADCFM) = (SOLVER == TFODE_SOLVER_DANTZIG) ? cfm_h : Ad * cfm_h;   // the dense solver wants cfm / h itself on A's diagonal
         // c is consumed: its slot now holds the row's two pre-decoded sweep-queue entries (body 1's lane | body 2's lane << 16)
         ROWF(S, r, ENT) = __int_as_float(pgs_make_entry(r, hdr, b1) | ((b2 < NB ? pgs_make_entry(r, hdr, b2) : (b1 << 8)) << 16));
       }
@@ -1052,7 +1125,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
         }
       }
       int offL[NISL], mL[NISL], baseL[NISL];
-      const int nshuf = (cfg.pgs_iters + 7) >> 3;
+      const int nshuf = (SOLVER == TFODE_SOLVER_DANTZIG) ? 0 : (cfg.pgs_iters + 7) >> 3;   // dWorldStep draws no random numbers
       { int acc = 0, draws = 0;
 #pragma unroll
         for (int L = 0; L < NISL; L++) { mL[L] = cntN[L] + cntF[L]; offL[L] = acc; acc += mL[L]; baseL[L] = draws; draws += nshuf * max(mL[L] - 1, 0); }
@@ -1087,7 +1160,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
       // Reorder 0 of every island (ODE shuffles before the first sweep).  The draws depend on the stream position only, so
       // all 32 lanes compute them at once (LCG jump-ahead to each draw's position) into the dead contact list; the swap
       // chain itself, the sequential part of Fisher-Yates, then runs with one leader lane per island.
-      {
+      if constexpr (SOLVER != TFODE_SOLVER_DANTZIG) {
         unsigned char* dr = reinterpret_cast<unsigned char*>(&S.cont[0][0]);
         const uint32_t seed_now = S.c.lcg_seed;
 #pragma unroll 1
@@ -1127,7 +1200,8 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
     PT_MARK(2)
 
     // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
-    if (wid < PGS_WARPS) pgs_bodylane(sm, cfg.pgs_iters, wid, lane);
+    if (SOLVER == TFODE_SOLVER_DANTZIG) { if (S.pgs_on) dantzig_env(S, P, env, lane); }
+    else if (wid < PGS_WARPS) pgs_bodylane(sm, cfg.pgs_iters, wid, lane);
     else if (cfg.pgs_iters > 8) pgs_helper(sm, cfg.pgs_iters, wid - PGS_WARPS, lane);   // permutations of the later reorders, off the sweeps' path
     PT_MARK(3)
     __syncthreads();

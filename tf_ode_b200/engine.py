@@ -20,7 +20,7 @@ EXPORTS = [
     "tfode_batch_config_default", "tfode_batch_create", "tfode_batch_destroy", "tfode_last_error",
     "tfode_batch_set_stream", "tfode_batch_reset", "tfode_batch_set_actions", "tfode_batch_set_speed",
     "tfode_batch_load_policy", "tfode_batch_step", "tfode_batch_observe", "tfode_batch_pack_rollout", "tfode_batch_get_bodies",
-    "tfode_batch_drain_transitions", "tfode_batch_contact_stats", "tfode_batch_rollout_host", "tfode_batch_get_state",
+    "tfode_batch_drain_transitions", "tfode_batch_contact_stats", "tfode_batch_lcp_failures", "tfode_batch_rollout_host", "tfode_batch_get_state",
     "tfode_batch_set_state", "tfode_batch_launch_count", "tfode_batch_n_envs", "tfode_batch_sync",
     "tfode_policy_infer",
     "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
@@ -59,6 +59,7 @@ def load_library():
     L.tfode_batch_pack_rollout.argtypes = [vp, vp]
     L.tfode_batch_drain_transitions.argtypes = [vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.tfode_batch_contact_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i32]
+    L.tfode_batch_lcp_failures.argtypes = [vp, C.POINTER(i64)]
     L.tfode_batch_rollout_host.argtypes = [vp, vp, i32, vp, vp, vp]
     L.tfode_batch_get_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
     L.tfode_batch_set_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
@@ -264,6 +265,11 @@ class RoverBatch:
         over, mx = C.c_int64(0), C.c_int64(0)
         self._ck(self.L.tfode_batch_contact_stats(self.h, C.byref(over), C.byref(mx), int(reset)))
         return over.value, mx.value
+
+    def lcp_failures(self):
+        n = C.c_int64(0)
+        self._ck(self.L.tfode_batch_lcp_failures(self.h, C.byref(n)))
+        return n.value
 
     def rollout_host(self, actions, n_substeps, obs, reward, done):
         """Host-buffer round trip (numpy arrays): H2D actions -> n steps -> D2H observations."""
