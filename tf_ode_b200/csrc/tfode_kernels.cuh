@@ -6,6 +6,9 @@
 namespace tfode {
 
 constexpr int WARPS_PER_CTA = 4;   // reset kernel
+#ifndef TFODE_EXP
+#define TFODE_EXP 0   // developer timing experiments of the lock-step body (tools/gpu_exp.sh); 0 = product
+#endif
 #ifndef TFODE_ENVS_PER_CTA
 #define TFODE_ENVS_PER_CTA 8
 #endif
@@ -266,6 +269,11 @@ __device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const f
   const int row = entry & 127;
   const float2* Jp = reinterpret_cast<const float2*>(&S.rowJ[row][(entry & BR_IS1) ? 0 : 6]);
   const float2 j0 = Jp[0], j1 = Jp[1], j2 = Jp[2];
+#if TFODE_EXP == 11   // sensitivity experiment (results unchanged): the three Jacobian loads once more
+  { const unsigned ja = (unsigned)__cvta_generic_to_shared(Jp); float d0, d1, d2, d3, d4, d5;
+    asm volatile("ld.shared.v2.f32 {%0,%1}, [%6]; ld.shared.v2.f32 {%2,%3}, [%6+8]; ld.shared.v2.f32 {%4,%5}, [%6+16];" : "=f"(d0), "=f"(d1), "=f"(d2), "=f"(d3), "=f"(d4), "=f"(d5) : "r"(ja));
+    asm volatile("" ::"f"(d0), "f"(d2), "f"(d4)); }
+#endif
 #ifdef TFODE_ROWS_AOS
   const float4 s0 = *reinterpret_cast<const float4*>(&S.rowS[row][0]);       // rhs Ad Adcfm lo
   const float2 s1 = *reinterpret_cast<const float2*>(&S.rowS[row][RS_HI]);   // hi lambda
@@ -273,6 +281,11 @@ __device__ __forceinline__ void pgs_load_row(const WarpSm& S, int entry, const f
 #else
   const float4 s0 = S.rowC[row];    // rhs Ad Adcfm lo
   const float2 s1 = S.rowHL[row];   // hi lambda
+#if TFODE_EXP == 16   // sensitivity experiment: the two row-scalar loads once more
+  { const unsigned ca = (unsigned)__cvta_generic_to_shared(&S.rowC[row]), ha = (unsigned)__cvta_generic_to_shared(&S.rowHL[row]); float d0, d1, d2, d3, d4, d5;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%6]; ld.shared.v2.f32 {%4,%5}, [%7];" : "=f"(d0), "=f"(d1), "=f"(d2), "=f"(d3), "=f"(d4), "=f"(d5) : "r"(ca), "r"(ha));
+    asm volatile("" ::"f"(d0), "f"(d4)); }
+#endif
 #endif
   r.meta = entry;
   r.hi = s1.x; lam = s1.y;
@@ -522,6 +535,9 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         const float other = __shfl_sync(FULLMASK, part, pl);
         const float lam_o = __shfl_sync(FULLMASK, lam, pl);
         const float lamf_o = __shfl_sync(FULLMASK, lamf, pl);
+#if TFODE_EXP == 13   // sensitivity experiment: two more shuffles (off the dependent chain)
+        { const float x1 = __shfl_sync(FULLMASK, rb.rhs, pl), x2 = __shfl_sync(FULLMASK, rb.Ad, pl); asm volatile("" ::"f"(x1), "f"(x2)); }
+#endif
         const float lam_c = is1 ? lam : lam_o, lamf_c = is1 ? lamf : lamf_o;
         float lo = rb.lo, hi = rb.hi;
         if (fric) { hi = fabsf(hi * lamf_c); lo = -hi; }
@@ -530,7 +546,17 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
         float nl = lam_c + delta;
         if (nl < lo) { delta = lo - lam_c; nl = lo; }
         else if (nl > hi) { delta = hi - lam_c; nl = hi; }
+#if TFODE_EXP == 15   // sensitivity experiment: four dependent adds of -0 ON the chain fc -> delta -> fc (+16 cycles of latency, same value)
+        { float mz = __int_as_float(0x80000000 | (threadIdx.x >> 10)); asm volatile("add.f32 %0, %0, %1; add.f32 %0, %0, %1; add.f32 %0, %0, %1; add.f32 %0, %0, %1;" : "+f"(delta) : "f"(mz)); }
+#endif
+#if TFODE_EXP == 14   // sensitivity experiment: sixteen ALU instructions off the chain (issue slots only)
+        { float z = rb.rhs; asm volatile("add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0;"
+                                         "add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0; add.f32 %0, %0, %0;" : "+f"(z)); asm volatile("" ::"f"(z)); }
+#endif
         if (fire && is1) ROWF(S, row, LAM) = nl;
+#if TFODE_EXP == 12   // sensitivity experiment: the lambda store once more (same value, same address)
+        if (fire && is1) { volatile float* lv = &ROWF(S, row, LAM); *lv = nl; }
+#endif
         const float dm = delta * invM;
         const float f0 = tfn::fma(dm, rb.J[0], fc[0]), f1 = tfn::fma(dm, rb.J[1], fc[1]), f2 = tfn::fma(dm, rb.J[2], fc[2]);
         const float f3 = tfn::fma(delta, rb.a[0], fc[3]), f4 = tfn::fma(delta, rb.a[1], fc[4]), f5 = tfn::fma(delta, rb.a[2], fc[5]);
