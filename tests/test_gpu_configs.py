@@ -176,3 +176,23 @@ def test_long_horizon_episode_statistics_against_double_oracle(scene):
     over, mx = g.contact_stats()
     assert over == 0, "contacts dropped in %d sub-steps (max generated %d)" % (over, mx)
     g.close(); o.close()
+
+
+def test_external_commands_on_crawlers_clamp_at_each_rover_own_amplitude():
+    """SetBoggieTorque clamps at boggie_max_torque, which Crawler_1's constructor sets to ITS torque amplitude (src/rover_1_crawlers.cc:22) --
+    jittered per environment in config 4.  Commands re-issued every 100 sub-steps, as bench.py does (found by bench.py --verify)."""
+    n = 256
+    g = RoverBatch(bench.make_cfg("config4", n)); o = oracle_lib.Oracle(bench.make_cfg("config4", n), "float", threads=8)
+    amps = np.array([g.get_state(e).crawler_amp for e in range(n)])
+    assert amps.min() < 21 and amps.max() > 29
+    for k in range(10):
+        a = bench.action_tape(0, k, n)
+        g.set_actions(torch.from_numpy(a).cuda()); o.set_actions(a)
+        if k == 0:
+            tq = np.array([g.get_state(e).boggie_torque for e in range(n)])
+            assert np.array_equal(tq, np.array([o.get_state(e).boggie_torque for e in range(n)])) and (np.abs(tq) <= amps + 1e-9).all()
+            assert (np.abs(a[:, 1]) > amps).any()    # the tape does ask for more than some rovers allow
+        g.step(100); o.step(100)
+    for e in range(n):
+        assert np.array_equal(oracle_lib.state_bodies(g.get_state(e))[:10], oracle_lib.state_bodies(o.get_state(e))[:10]), e
+    g.close(); o.close()

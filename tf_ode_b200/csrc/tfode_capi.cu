@@ -400,8 +400,7 @@ int tfode_batch_set_actions(TfodeBatch* b, const float* actions_dev) {
   if (!b || !actions_dev) return TFODE_EINVAL;
   GUARD(b);
   const int n = b->cfg.n_envs;
-  const float bmax = b->cfg.controller == TFODE_CTRL_CRAWLER ? b->cfg.crawler_amp : 25.0f;
-  set_actions_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, actions_dev, bmax);
+  set_actions_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, actions_dev, b->cfg.controller == TFODE_CTRL_CRAWLER ? 1 : 0);
   b->launches++;
   CK(cudaGetLastError());
   return TFODE_OK;

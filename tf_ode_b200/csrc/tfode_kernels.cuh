@@ -1619,11 +1619,14 @@ __global__ void bodies_kernel(const EnvRec* rec, int n, float* out) {
   float* o = out + (size_t)i * 13;
   for (int k = 0; k < 13; k++) o[k] = r.body[k][b];
 }
-__global__ void set_actions_kernel(EnvRec* rec, int n, const float* act, float bmax) {
+__global__ void set_actions_kernel(EnvRec* rec, int n, const float* act, int crawler) {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= n) return;
+  // boggie_max_torque is 25 (src/rover_1.cc:50) except for Crawler_1, whose constructor sets it to ITS torque amplitude
+  // (src/rover_1_crawlers.cc:22) -- per environment here, since BASELINE config 4 jitters the amplitude
+  const double bmax = crawler ? (double)rec[e].c.cr_amp : 25.0;
   rec[e].c.steering_rate = fmin(fmax(-15.0, (double)act[e * 2]), 15.0);          // SetSteeringRate, src/rover_1.cc:326-329
-  rec[e].c.boggie_torque = fmin(fmax(-(double)bmax, (double)act[e * 2 + 1]), (double)bmax);  // SetBoggieTorque :338-341
+  rec[e].c.boggie_torque = fmin(fmax(-bmax, (double)act[e * 2 + 1]), bmax);  // SetBoggieTorque :338-341
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -13,7 +13,7 @@ import numpy as np
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libtfode_b200.so")
+LIB_PATH = os.environ.get("TFODE_LIB") or os.path.join(_HERE, "csrc", "libtfode_b200.so")   # TFODE_LIB: developer override (A/B variants built by tools/build_variant.sh)
 _LIB = None
 
 EXPORTS = [
