@@ -44,6 +44,7 @@ struct TfodeBatch {
   float* h_pin = nullptr; size_t h_pin_bytes = 0;
   int* d_ids = nullptr; int ids_cap = 0;
   size_t smem_bytes = 0, smem_step = 0;
+  int lsu = 2;   // lock-step unroll factor of the step_kernel instantiation this batch launches (4 on the bare plane)
 };
 
 // Every entry point that takes a handle runs on the handle's own device, whatever device the calling thread had current
@@ -357,8 +358,11 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   b->cfg.hf_heights = nullptr;
   b->smem_bytes = sizeof(WarpSm) * WARPS_PER_CTA;
   b->smem_step = sizeof(WarpSm) * ENVS_PER_CTA;
-  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
-  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_DANTZIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
+  b->lsu = cfg->scene == TFODE_SCENE_PLANE ? 4 : 2;
+  if (const char* o = std::getenv("TFODE_LSU")) b->lsu = std::atoi(o) == 4 ? 4 : 2;   // developer override for A/B runs
+  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
+  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
+  CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_DANTZIG, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
   if (launch_reset(b, nullptr, n, 1) != TFODE_OK) return fail(TFODE_ECUDA);
   CKC(cudaStreamSynchronize(b->stream));
@@ -468,8 +472,11 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
     StepParams P = b->P;
     P.set_budget = (r == 0) ? n_substeps : -1;
     const dim3 grid((n + ENVS_PER_CTA - 1) / ENVS_PER_CTA), block(ENVS_PER_CTA * 32);
-    if (b->cfg.solver == TFODE_SOLVER_DANTZIG) step_kernel<TFODE_SOLVER_DANTZIG><<<grid, block, b->smem_step, b->stream>>>(P);
-    else step_kernel<TFODE_SOLVER_QUICKSTEP><<<grid, block, b->smem_step, b->stream>>>(P);
+    // Instantiation by measurement (profiles/r02_ab_table.md): the lock-step loop unrolled by 4 where sweeps are short (bare plane: ~4 contacts),
+    // by 2 where they are long (step boxes, heightfields) -- the loop's instruction footprint against its per-iteration overhead.
+    if (b->cfg.solver == TFODE_SOLVER_DANTZIG) step_kernel<TFODE_SOLVER_DANTZIG, 2><<<grid, block, b->smem_step, b->stream>>>(P);
+    else if (b->lsu == 4) step_kernel<TFODE_SOLVER_QUICKSTEP, 4><<<grid, block, b->smem_step, b->stream>>>(P);
+    else step_kernel<TFODE_SOLVER_QUICKSTEP, 2><<<grid, block, b->smem_step, b->stream>>>(P);
     b->launches++;
     CK(cudaGetLastError());
     if (mlp && !fused_actor) {

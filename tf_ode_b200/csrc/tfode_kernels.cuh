@@ -6,6 +6,14 @@
 namespace tfode {
 
 constexpr int WARPS_PER_CTA = 4;   // reset kernel
+// Code-size switch (A/B): the reorder helpers as real functions instead of three inlined copies each (measured slower).
+#ifdef TFODE_NOINLINE_REORDER
+#define TFODE_REORDER_INLINE __noinline__
+#else
+#define TFODE_REORDER_INLINE __forceinline__
+#endif
+#define TFODE_PRAGMA_(x) _Pragma(#x)
+#define TFODE_UNROLL(n) TFODE_PRAGMA_(unroll n)
 #ifndef TFODE_EXP
 #define TFODE_EXP 0   // developer timing experiments of the lock-step body (tools/gpu_exp.sh); 0 = product
 #endif
@@ -316,7 +324,7 @@ __device__ __forceinline__ unsigned char* ord_buffer(WarpSm& S, int off, int r, 
 }
 // RANDOMLY_REORDER_CONSTRAINTS: Fisher-Yates with ODE's dRandInt on this island's slice of the environment's stream (one lane).
 // The draw of the next swap (LCG step, bit folds, reciprocal-multiply modulo) overlaps the shared-memory round trip of this one.
-__device__ __forceinline__ void fy_shuffle(unsigned char* o, int stride, int m, uint32_t seed0, int base, int r) {
+__device__ TFODE_REORDER_INLINE void fy_shuffle(unsigned char* o, int stride, int m, uint32_t seed0, int base, int r) {
   uint32_t sd = lcg_jump(seed0, (uint32_t)(base + r * (m - 1)));
   int sw = lcg_randint(sd, 2u);
   for (int q = 1; q < m; q++) {
@@ -346,7 +354,7 @@ __device__ __forceinline__ unsigned* pgs_handover(WarpSm& S, int r) { return rei
 //  * schedule: which lock-step a row fires at depends only on the queues (a row fires when it heads the queues of both of its
 //    bodies), not on any value, so the integer part of the lock-step loop is run once per reorder: bit t of `mask0` = this
 //    lane relaxes its next queue entry at lock-step t; T = lock-steps per sweep (warp-uniform).
-__device__ __forceinline__ void pgs_fill_sched(const WarpSm& S, const unsigned char* ord, int ostride, int m, int b, int hbase,
+__device__ TFODE_REORDER_INLINE void pgs_fill_sched(const WarpSm& S, const unsigned char* ord, int ostride, int m, int b, int hbase,
                                                unsigned short* myq, int qn, int dummy_ent, unsigned long long& mask0, int& T) {
   unsigned short* qw = myq;
   int k = 0;
@@ -373,7 +381,7 @@ __device__ __forceinline__ void pgs_fill_sched(const WarpSm& S, const unsigned c
   }
 }
 // rows of body b in its island (does not depend on the permutation) and the start of its queue inside a queue buffer
-__device__ __forceinline__ void pgs_queue_extent(const WarpSm& S, const unsigned char* ordA, int m, int b, int& qn, int& qoff) {
+__device__ TFODE_REORDER_INLINE void pgs_queue_extent(const WarpSm& S, const unsigned char* ordA, int m, int b, int& qn, int& qoff) {
   qn = 0;
   for (int k = 0; k < m; k++) {
     const int pk = __float_as_int(ROWF(S, ordA[k], ENT));
@@ -446,6 +454,7 @@ __device__ void pgs_helper(WarpSm* sm, int pgs_iters, int p, int lane) {
   }
 }
 
+template <int LSU>   // unroll factor of the lock-step loop
 __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
   const int e = pgs_env_of(sm, wid, lane), b = lane & 15;
   int hbase = lane & 16;
@@ -567,20 +576,28 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
       };
       const unsigned short* qp0 = myq;
       const int e_first = (mask32 & 1u) ? (int)myq[0] : dummy_ent;
-      for (int sw_i = 0; sw_i < nsw; sw_i++) {
-        unsigned mrem = mask32;
-        const unsigned short* qp = qp0;
-#pragma unroll 4
-        for (int t = 0; t < T - 1; t++) {
-          const bool fire = (mrem & 1u) != 0u;
-          qp += fire ? 1 : 0;
-          mrem >>= 1;
-          int en = dummy_ent;
-          if (mrem & 1u) en = *qp;
-          lock_step(fire, en);
-        }
-        lock_step((mrem & 1u) != 0u, e_first);   // last lock-step of the sweep: the next one is lock-step 0 again
+      // The sweeps of this reorder block.  The unroll factor of the lock-step loop trades loop overhead against the loop's instruction
+      // footprint (main body x U + remainder body + peeled last step, ~100 instructions each): measured on every workload
+      // (profiles/r02_ab_table.md), 2 wins by 6-10 % where sweeps are long (step boxes, wheels in the groove), 4 by 2 % where they are short
+      // (plane).  Both loops inside one kernel lose to either (the footprint doubles), so LSU is a template parameter of step_kernel and the
+      // launcher picks the instantiation by scene.
+#define TFODE_SWEEP_LOOPS(U)                                                                                                  \
+      for (int sw_i = 0; sw_i < nsw; sw_i++) {                                                                                \
+        unsigned mrem = mask32;                                                                                               \
+        const unsigned short* qp = qp0;                                                                                       \
+        TFODE_UNROLL(U)                                                                                                       \
+        for (int t = 0; t < T - 1; t++) {                                                                                     \
+          const bool fire = (mrem & 1u) != 0u;                                                                                \
+          qp += fire ? 1 : 0;                                                                                                 \
+          mrem >>= 1;                                                                                                         \
+          int en = dummy_ent;                                                                                                 \
+          if (mrem & 1u) en = *qp;                                                                                            \
+          lock_step(fire, en);                                                                                                \
+        }                                                                                                                     \
+        lock_step((mrem & 1u) != 0u, e_first);   /* last lock-step of the sweep: the next one is lock-step 0 again */         \
       }
+      TFODE_SWEEP_LOOPS(LSU)
+#undef TFODE_SWEEP_LOOPS
     } else {
     // Fallback (more than 32 lock-steps per sweep, or single-row chains): the same lock-steps with the readiness test done on
     // the fly -- queue entries pre-decoded, lambda owned by one lane and exchanged in the shuffle round, no __syncwarp.
@@ -646,7 +663,8 @@ __device__ void pgs_bodylane(WarpSm* sm, int pgs_iters, int wid, int lane) {
 #define TFODE_MODEL_SRC (*P.model)
 #endif
 // SOLVER: TFODE_SOLVER_QUICKSTEP (the fast path; no trace of the dense solver in its code) or TFODE_SOLVER_DANTZIG.
-template <int SOLVER>
+// LSU: unroll factor of the sweeps' lock-step loop (2 or 4, see pgs_bodylane; chosen per scene by the launcher).
+template <int SOLVER, int LSU>
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -1227,7 +1245,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
 
     // ---------------------------------------------------------------- PGS / SOR sweeps, packed over the CTA's environments
     if (SOLVER == TFODE_SOLVER_DANTZIG) { if (S.pgs_on) dantzig_env(S, P, env, lane); }
-    else if (wid < PGS_WARPS) pgs_bodylane(sm, cfg.pgs_iters, wid, lane);
+    else if (wid < PGS_WARPS) pgs_bodylane<LSU>(sm, cfg.pgs_iters, wid, lane);
     else if (cfg.pgs_iters > 8) pgs_helper(sm, cfg.pgs_iters, wid - PGS_WARPS, lane);   // permutations of the later reorders, off the sweeps' path
     PT_MARK(3)
     __syncthreads();
