@@ -196,3 +196,24 @@ def test_external_commands_on_crawlers_clamp_at_each_rover_own_amplitude():
     for e in range(n):
         assert np.array_equal(oracle_lib.state_bodies(g.get_state(e))[:10], oracle_lib.state_bodies(o.get_state(e))[:10]), e
     g.close(); o.close()
+
+
+def test_persistent_launch_equals_plain_launch(monkeypatch):
+    """Batches larger than one wave of resident CTAs are stepped by a persistent grid pulling (group, 25-sub-step slice) items; the records it
+    leaves are bit-identical to the plain one-CTA-per-group launch (TFODE_PERSISTENT=0), whatever the call length and the batch size."""
+    for workload, n, calls in (("config2", 4096, (100, 37, 263)), ("config4", 8192 + 24, (500,)), ("config3", 3000, (130, 270))):
+        outs = []
+        for persistent in ("1", "0"):
+            monkeypatch.setenv("TFODE_PERSISTENT", persistent)
+            g = RoverBatch(bench.make_cfg(workload, n))
+            if g.cfg.controller == abi.CTRL_MLP:
+                g.load_policy(glorot_policy())
+            g.set_actions(torch.from_numpy(bench.action_tape(0, 1, n)).cuda())
+            for k in calls:
+                g.step(k)
+            out = torch.zeros(n, 12, 13, device="cuda"); g.get_bodies(out)
+            rows = torch.zeros(n, abi.ROLLOUT_WIDTH, device="cuda"); g.pack_rollout(rows)
+            outs.append((out.clone(), rows.clone(), g.get_state(n - 1).lcg_seed, g.get_state(5).time_steps))
+            g.close()
+        assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1]) and outs[0][2:] == outs[1][2:], workload
+        assert outs[0][3] == sum(calls)

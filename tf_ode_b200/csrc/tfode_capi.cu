@@ -28,6 +28,9 @@ struct TfodeBatch {
   float* hf_h = nullptr; float* hf_bmax = nullptr;
   float* policy_in = nullptr; int* parked_list = nullptr; int* n_parked = nullptr;
   float* trans = nullptr; int* n_trans = nullptr; int trans_cap = 0;
+  int* sched = nullptr;   // [0] item counter, [1 .. 1 + n_groups) finished slices per group (persistent launches)
+  int resident_ctas = 0;  // CTAs of step_kernel that are co-resident on this device
+  int persistent = 1;     // TFODE_PERSISTENT=0 turns the persistent launch off (A/B)
   float* lcp_f = nullptr; int* lcp_i = nullptr;   // TFODE_SOLVER_DANTZIG scratch
   unsigned long long* cstats = nullptr;   // contact-capacity audit counters (StepParams::cstats)
   float* ext_speed = nullptr;
@@ -267,6 +270,8 @@ int tfode_sizeof_config() { return (int)sizeof(TfodeBatchConfig); }
 int tfode_sizeof_state() { return (int)sizeof(TfodeEnvState); }
 int tfode_sizeof_record() { return (int)sizeof(EnvRec); }
 
+constexpr int TFODE_SLICE_LEN = 25;   // sub-steps per work item of a persistent launch
+
 static int launch_reset(TfodeBatch* b, const int* d_ids, int n, int first) {
   reset_kernel<<<launch_blocks(n), WARPS_PER_CTA * 32, b->smem_bytes, b->stream>>>(b->P, d_ids, n, first);
   b->launches++;
@@ -358,12 +363,23 @@ int tfode_batch_create(const TfodeBatchConfig* cfg, TfodeBatch** out) {
   b->cfg.hf_heights = nullptr;
   b->smem_bytes = sizeof(WarpSm) * WARPS_PER_CTA;
   b->smem_step = sizeof(WarpSm) * ENVS_PER_CTA;
+  {
+    const int groups = (n + ENVS_PER_CTA - 1) / ENVS_PER_CTA;
+    CKC(cudaMalloc(&b->sched, sizeof(int) * (size_t)(groups + 1)));
+    if (const char* o = std::getenv("TFODE_PERSISTENT")) b->persistent = std::atoi(o);
+  }
   b->lsu = cfg->scene == TFODE_SCENE_PLANE ? 4 : 2;
   if (const char* o = std::getenv("TFODE_LSU")) b->lsu = std::atoi(o) == 4 ? 4 : 2;   // developer override for A/B runs
   CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_QUICKSTEP, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(step_kernel<TFODE_SOLVER_DANTZIG, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_step));
   CKC(cudaFuncSetAttribute(reset_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b->smem_bytes));
+  {
+    int per_sm = 0;
+    if (b->lsu == 4) CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_kernel<TFODE_SOLVER_QUICKSTEP, 4>, ENVS_PER_CTA * 32, b->smem_step));
+    else CKC(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, step_kernel<TFODE_SOLVER_QUICKSTEP, 2>, ENVS_PER_CTA * 32, b->smem_step));
+    b->resident_ctas = cfg->solver == TFODE_SOLVER_QUICKSTEP ? per_sm * prop.multiProcessorCount : 0;   // the dense-solver path keeps the plain launch
+  }
   if (launch_reset(b, nullptr, n, 1) != TFODE_OK) return fail(TFODE_ECUDA);
   CKC(cudaStreamSynchronize(b->stream));
   *out = b;
@@ -376,7 +392,7 @@ void tfode_batch_destroy(TfodeBatch* b) {
   DeviceGuard guard_(b);
   for (int t = 0; t < 2; t++) { cudaFree(b->tree_nodes[t]); cudaFree(b->tree_params[t]); }
   cudaFree(b->rec); cudaFree(b->budget); cudaFree(b->hf_h); cudaFree(b->hf_bmax); cudaFree(b->policy_in); cudaFree(b->parked_list);
-  cudaFree(b->n_parked); cudaFree(b->cstats); cudaFree(b->lcp_f); cudaFree(b->lcp_i); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
+  cudaFree(b->sched); cudaFree(b->n_parked); cudaFree(b->cstats); cudaFree(b->lcp_f); cudaFree(b->lcp_i); cudaFree(b->trans); cudaFree(b->ext_speed); cudaFree(b->ring4); cudaFree(b->model_g); cudaFree(b->weights); cudaFree(b->d_obs); cudaFree(b->d_rew);
   cudaFree(b->d_done); cudaFree(b->d_act); cudaFree(b->d_ids);
   policy_tc_free(b->tc);
   if (b->h_pin) cudaFreeHost(b->h_pin);
@@ -471,7 +487,17 @@ int tfode_batch_step(TfodeBatch* b, int n_substeps) {
   for (int r = 0; r < rounds; r++) {
     StepParams P = b->P;
     P.set_budget = (r == 0) ? n_substeps : -1;
-    const dim3 grid((n + ENVS_PER_CTA - 1) / ENVS_PER_CTA), block(ENVS_PER_CTA * 32);
+    const int groups = (n + ENVS_PER_CTA - 1) / ENVS_PER_CTA;
+    dim3 grid(groups), block(ENVS_PER_CTA * 32);
+    // Persistent launch: when the groups do not fit one wave of resident CTAs and nothing parks, one wave of CTAs pulls (group, 25-sub-step
+    // slice) items instead, so the last wave of a call is as full as the others (config 2: 512 groups on 296 slots = 1.73 waves, not 2).
+    P.slice_len = 0;
+    if (b->persistent && rounds == 1 && b->resident_ctas > 0 && groups > b->resident_ctas && groups < 16 * b->resident_ctas && n_substeps > TFODE_SLICE_LEN) {   // beyond 16 waves the tail is < 3 % and not worth the slices' record traffic
+      P.slice_len = TFODE_SLICE_LEN; P.n_groups = groups; P.n_items = groups * ((n_substeps + TFODE_SLICE_LEN - 1) / TFODE_SLICE_LEN);
+      P.sched = b->sched; P.slice_done = b->sched + 1;
+      CK(cudaMemsetAsync(b->sched, 0, sizeof(int) * (size_t)(groups + 1), b->stream));
+      grid = dim3(b->resident_ctas);
+    }
     // Instantiation by measurement (profiles/r02_ab_table.md): the lock-step loop unrolled by 4 where sweeps are short (bare plane: ~4 contacts),
     // by 2 where they are long (step boxes, heightfields) -- the loop's instruction footprint against its per-iteration overhead.
     if (b->cfg.solver == TFODE_SOLVER_DANTZIG) step_kernel<TFODE_SOLVER_DANTZIG, 2><<<grid, block, b->smem_step, b->stream>>>(P);

@@ -113,6 +113,8 @@ struct StepParams {
   unsigned long long* cstats;   // [2]: islands whose Dantzig drive stalled (TFODE_SOLVER_DANTZIG)
   // TFODE_SOLVER_DANTZIG scratch: LCP_ROW_F floats and LCP_ROW_I ints per row slot, MAXROWS row slots per environment (global memory)
   float* lcp_f; int* lcp_i;
+  // persistent launch (slice_len > 0): item counter, per-group count of finished slices, item geometry
+  int* sched; int* slice_done; int slice_len, n_items, n_groups;
   // external commands
   const float* ext_speed;  // NULL or [n_envs]
   // tire-sphere centres in the wheel frame (Model::ring, padded to float4) in global memory: the lanes of a warp read 32

@@ -668,16 +668,41 @@ template <int SOLVER, int LSU>
 __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_kernel(const StepParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  const int env = blockIdx.x * ENVS_PER_CTA + wid;
-  const bool valid = env < P.n_envs;
   WarpSm* const sm = reinterpret_cast<WarpSm*>(smem_raw);
   WarpSm& S = sm[wid];
   const Model& M = TFODE_MODEL_SRC;   // A/B switch: constant memory (g_model) or the global-memory copy (*P.model)
   const TfodeBatchConfig& cfg = P.cfg;
+
+  // Work items.  Plain launch (P.slice_len == 0): CTA b = environment group b for the whole call.  Persistent launch: the grid is one
+  // wave of co-resident CTAs pulling (group, slice) items -- slice_len sub-steps of one group of 8 environments -- from an atomic
+  // counter in slice-major order, so that a batch of, say, 1.73 waves of groups costs 1.73 waves of time instead of 2.  A group's
+  // slices are sequential: item (g, s) waits for slice_done[g] == s.  The item it waits for has a smaller index, was therefore
+  // claimed earlier by a CTA that is resident and itself only waits on smaller indices, so the wait always ends.
+  for (;;) {
+  int group = blockIdx.x, slice = 0;
+  if (P.slice_len > 0) {
+    __syncthreads();   // every warp is done with the previous item's shared memory
+    if (threadIdx.x == 0) {
+      const int item = atomicAdd(P.sched, 1);
+      int g_ = -1, s_ = 0;
+      if (item < P.n_items) {
+        g_ = item % P.n_groups; s_ = item / P.n_groups;
+        while (ld_acquire(P.slice_done + g_) < s_) __nanosleep(256);
+      }
+      sm[0].aux[8] = __int_as_float(g_); sm[0].aux[9] = __int_as_float(s_);
+    }
+    __syncthreads();
+    group = __float_as_int(sm[0].aux[8]); slice = __float_as_int(sm[0].aux[9]);
+    if (group < 0) return;   // CTA-uniform: the queue is empty
+  }
+  const int env = group * ENVS_PER_CTA + wid;
+  const bool valid = env < P.n_envs;
   const uint32_t env_global = (uint32_t)(cfg.env_id_offset + env);
+  const bool first_slice = P.set_budget >= 0 && slice == 0;
+  int slice_left = P.slice_len > 0 ? P.slice_len : 0x7fffffff;
 
   int budget = 0;
-  if (valid) budget = (P.set_budget >= 0) ? P.set_budget : P.budget[env];
+  if (valid) budget = first_slice ? P.set_budget : P.budget[env];
   if (lane == 0) { S.pgs_on = 0; S.c.frozen = 0; S.c.parked = 0; S.cap_over = 0; S.cap_max = 0; }
 
   // ---------------------------------------------------------------- load the record (coalesced float4 -> smem staging -> registers)
@@ -703,7 +728,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
       for (int i = lane; i < (int)(sizeof(Ctrl) / 4); i += 32) cd[i] = cs[i];
     }
     __syncwarp();
-    if (P.set_budget >= 0 && lane == 0) S.c.done_call = 0;
+    if (first_slice && lane == 0) S.c.done_call = 0;
     quatToR(R, q);
     publish_body(S, lane, pos, q, R, lvel, avel);
     __syncwarp();
@@ -731,7 +756,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
   for (;;) {
     __syncwarp();
     if (valid && S.c.frozen) budget = 0;
-    const bool runnable = valid && budget > 0 && S.c.parked != 1;
+    const bool runnable = valid && budget > 0 && slice_left > 0 && S.c.parked != 1;
     if (!__syncthreads_or(runnable ? 1 : 0)) break;
     const bool do_part_a = runnable && S.c.parked == 0;
 
@@ -1504,7 +1529,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
     }
     __syncwarp();
 
-    budget--;
+    budget--; slice_left--;
     if (__float_as_int(S.aux[4]) != 0 && cfg.auto_reset) {
       const uint32_t ep = S.c.episode + 1;
       __syncwarp();
@@ -1523,7 +1548,7 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
   PT_FLUSH
   // ---------------------------------------------------------------- store the record
   __syncwarp();
-  if (!valid) return;
+  if (valid) {
   if (lane == 0) {
     P.budget[env] = budget;
     if (S.cap_over) atomicAdd(P.cstats, (unsigned long long)S.cap_over);
@@ -1545,6 +1570,12 @@ __global__ void __launch_bounds__(ENVS_PER_CTA * 32, 16 / ENVS_PER_CTA) step_ker
     float4* dst = reinterpret_cast<float4*>(grec);
     constexpr int N4 = sizeof(EnvRec) / 16;
     for (int i = lane; i < N4; i += 32) dst[i] = src[i];
+  }
+  }
+  if (P.slice_len <= 0) return;
+  __threadfence();     // this item's records are visible device-wide ...
+  __syncthreads();
+  if (threadIdx.x == 0) st_release(P.slice_done + group, slice + 1);   // ... before the group's next slice may be claimed
   }
 }
 

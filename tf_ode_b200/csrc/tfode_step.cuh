@@ -78,6 +78,10 @@ enum { RS_RHS = 0, RS_AD = 1, RS_ADCFM = 2, RS_LO = 3, RS_HI = 4, RS_LAM = 5, RS
 #define ROW_HDR_STRIDE 4
 #endif
 
+// ---------------------------------------------------------------- device-scope flags of the persistent work queue
+__device__ __forceinline__ int ld_acquire(const int* p) { int v; asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory"); return v; }
+__device__ __forceinline__ void st_release(int* p, int v) { asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
 // ---------------------------------------------------------------- small math
 // fma placement of these products is fixed by the numerics contract (include/tfode_numerics.h); the kernels are
 // compiled with -fmad=false, so every other expression below is evaluated exactly as written.
