@@ -276,6 +276,25 @@ int tfode_format_transition(const float* row_host, int kind, char* out, size_t c
  * the remaining multipliers at zero -- lcp.cpp's "s <= 0" exit.  0 in every tested scene. */
 int tfode_batch_lcp_failures(TfodeBatch* b, int64_t* stalled_islands);
 
+/* A stepping call that allocates nothing, for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * It is tfode_batch_step with the dense Dantzig solver (step_kernel<TFODE_SOLVER_DANTZIG>), whose per-island LCP work arrays --
+ * cudaMalloc'd at creation for a TFODE_SOLVER_DANTZIG handle, 211 KB per environment -- live here in a file-scope
+ * `static __device__` array of the library instead.  So a handle created with TFODE_SOLVER_QUICKSTEP (no dense-solver scratch)
+ * can take dWorldStep-equivalent steps, and the call itself makes no cudaMalloc / cudaFree / allocating library call:
+ *   actions_dev     DEVICE float [n,2] as tfode_batch_set_actions takes, or NULL to keep the current commands       (input)
+ *   n_substeps      sub-steps to run, >= 0
+ *   bodies_out_dev  DEVICE float [n,12,13] as tfode_batch_get_bodies writes, or NULL                                (output)
+ * all enqueued on the handle's stream, three launches at most.  Results are bit-identical to tfode_batch_set_actions +
+ * tfode_batch_step + tfode_batch_get_bodies on a TFODE_SOLVER_DANTZIG handle in the same state.
+ * Limits: n_envs <= TFODE_NOALLOC_MAX_ENVS (else TFODE_EINVAL with a message in tfode_last_error); controllers that park
+ * environments between launches (model trees, TFODE_POLICY_TC) are refused with TFODE_ESTATE.  The array (26.2 MiB) is held by every
+ * GPU that loads the library until the process exits.  All calls on one device share it -- from any handle or stream -- and it keeps
+ * the last call's contents (nothing in it needs clearing: every island writes its work arrays before reading them): two such
+ * calls that overlap on the GPU (different streams, no ordering between them) RACE and corrupt each other's solves. */
+#define TFODE_NOALLOC_MAX_ENVS 128
+int tfode_batch_step_dantzig_static(TfodeBatch* b, const float* actions_dev, int n_substeps, float* bodies_out_dev);
+
 /* Host-buffer round trip used by the end-to-end measurement: H2D actions (may be NULL),
  * n_substeps, D2H obs17/reward/done (HOST pointers, pinned or pageable; any may be NULL). */
 int tfode_batch_rollout_host(TfodeBatch* b, const float* actions_host, int n_substeps,

@@ -13,6 +13,7 @@ NACT = 2
 MLP_HIDDEN = 512
 TRANSITION_WIDTH = 40
 ROLLOUT_WIDTH = 24
+NOALLOC_MAX_ENVS = 128   # TFODE_NOALLOC_MAX_ENVS
 POLICY_NFLOATS = 17 * 512 + 512 + 512 * 512 + 512 + 512 * 2 + 2  # 272 898, scripts/rover_training_1.py:26-35
 
 SCENE_PLANE, SCENE_STEP_BOXES, SCENE_HEIGHTFIELD = 0, 1, 2

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -598,6 +599,80 @@ int tfode_batch_contact_stats(TfodeBatch* b, int64_t* over_capacity_steps, int64
   if (over_capacity_steps) *over_capacity_steps = (int64_t)h[0];
   if (max_generated) *max_generated = (int64_t)h[1];
   if (reset) CK(cudaMemsetAsync(b->cstats, 0, sizeof(h), b->stream));
+  return TFODE_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// tfode_batch_step_dantzig_static: the dense-solver step with its LCP scratch in a file-scope device array instead of
+// cudaMalloc'd memory, for callers that may not allocate (include/tfode_batch.h).  No counterpart in the reference.
+// Every GPU that loads this library holds the array (26.2 MiB) until the process exits; every call on a device shares it.
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr size_t NOALLOC_F_BYTES = (size_t)TFODE_NOALLOC_MAX_ENVS * MAXROWS * LCP_ROW_F * sizeof(float);
+constexpr size_t NOALLOC_I_BYTES = (size_t)TFODE_NOALLOC_MAX_ENVS * MAXROWS * LCP_ROW_I * sizeof(int);
+static_assert(NOALLOC_F_BYTES % 256 == 0, "the int part of the static scratch must stay 256-byte aligned");
+constexpr int NOALLOC_MAX_DEVICES = 64;
+}
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_F_BYTES + NOALLOC_I_BYTES];
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not a device address: the address a kernel can use is looked
+// up once per device (each device has its own copy of the array) with that device current.
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+static int noalloc_scratch(TfodeBatch* b, unsigned char** out) {   // the caller holds GUARD(b): b's device is current
+  const int dev = b->cfg.device;
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) { b->err = "tfode_batch_step_dantzig_static: device index beyond " + std::to_string(NOALLOC_MAX_DEVICES - 1); return TFODE_EINVAL; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    cudaPointerAttributes at{};
+    CK(cudaPointerGetAttributes(&at, p));
+    if (!p || at.type != cudaMemoryTypeDevice || at.device != dev) { b->err = "tfode_batch_step_dantzig_static: the static scratch did not resolve to memory of this handle's device"; return TFODE_ECUDA; }
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = (unsigned char*)g_noalloc_ptr[dev];
+  return TFODE_OK;
+}
+
+int tfode_batch_step_dantzig_static(TfodeBatch* b, const float* actions_dev, int n_substeps, float* bodies_out_dev) {
+  if (!b || n_substeps < 0) return TFODE_EINVAL;
+  GUARD(b);
+  const int n = b->cfg.n_envs;
+  if (n > TFODE_NOALLOC_MAX_ENVS) {
+    b->err = "tfode_batch_step_dantzig_static: " + std::to_string(n) + " environments, the static scratch holds " + std::to_string(TFODE_NOALLOC_MAX_ENVS) +
+             " (use a TFODE_SOLVER_DANTZIG handle and tfode_batch_step beyond that)";
+    return TFODE_EINVAL;
+  }
+  const bool mlp = b->cfg.controller == TFODE_CTRL_MLP;
+  if (b->cfg.controller == TFODE_CTRL_MODEL_TREE || (mlp && b->cfg.policy_precision != TFODE_POLICY_FP32)) {
+    b->err = "tfode_batch_step_dantzig_static: controllers that park environments between launches (model trees, TFODE_POLICY_TC) are not served here";
+    return TFODE_ESTATE;
+  }
+  if (mlp && !b->has_policy) { b->err = "TFODE_CTRL_MLP needs tfode_batch_load_policy first"; return TFODE_ESTATE; }
+  unsigned char* scratch = nullptr;
+  if (int rc = noalloc_scratch(b, &scratch)) return rc;
+  if (actions_dev) {
+    set_actions_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(b->rec, n, actions_dev, b->cfg.controller == TFODE_CTRL_CRAWLER ? 1 : 0);
+    b->launches++;
+    CK(cudaGetLastError());
+  }
+  if (n_substeps > 0) {
+    // Nothing in the scratch has to start at zero: dantzig_env writes an island's rows and lcp_dantzig initialises its work arrays before
+    // reading them (the cudaMalloc'd scratch of the existing path starts uninitialised too), so the last call's contents are harmless.
+    StepParams P = b->P;
+    P.set_budget = n_substeps; P.slice_len = 0;
+    P.lcp_f = (float*)scratch; P.lcp_i = (int*)(scratch + NOALLOC_F_BYTES);
+    const int groups = (n + ENVS_PER_CTA - 1) / ENVS_PER_CTA;
+    step_kernel<TFODE_SOLVER_DANTZIG, 2><<<groups, ENVS_PER_CTA * 32, b->smem_step, b->stream>>>(P);
+    b->launches++;
+    CK(cudaGetLastError());
+  }
+  if (bodies_out_dev) {
+    bodies_kernel<<<(n * NB + 127) / 128, 128, 0, b->stream>>>(b->rec, n, bodies_out_dev);
+    b->launches++;
+    CK(cudaGetLastError());
+  }
   return TFODE_OK;
 }
 

@@ -26,6 +26,7 @@ EXPORTS = [
     "tfode_model_tree_parse", "tfode_batch_load_model_trees", "tfode_model_tree_infer", "tfode_batch_get_tree_nodes",
     "tfode_heightmap_load_png", "tfode_heightmap_decode_png", "tfode_free",
     "tfode_savedmodel_read_actor", "tfode_batch_load_policy_saved_model", "tfode_format_transition",
+    "tfode_batch_step_dantzig_static",
 ]
 
 
@@ -60,6 +61,7 @@ def load_library():
     L.tfode_batch_drain_transitions.argtypes = [vp, vp, i32, C.POINTER(i32), C.POINTER(i32)]
     L.tfode_batch_contact_stats.argtypes = [vp, C.POINTER(i64), C.POINTER(i64), i32]
     L.tfode_batch_lcp_failures.argtypes = [vp, C.POINTER(i64)]
+    L.tfode_batch_step_dantzig_static.argtypes = [vp, vp, i32, vp]
     L.tfode_batch_rollout_host.argtypes = [vp, vp, i32, vp, vp, vp]
     L.tfode_batch_get_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
     L.tfode_batch_set_state.argtypes = [vp, i32, C.POINTER(abi.EnvState)]
@@ -265,6 +267,13 @@ class RoverBatch:
         over, mx = C.c_int64(0), C.c_int64(0)
         self._ck(self.L.tfode_batch_contact_stats(self.h, C.byref(over), C.byref(mx), int(reset)))
         return over.value, mx.value
+
+    def step_dantzig_static(self, actions_dev, n_substeps, bodies_out_dev):
+        """tfode_batch_step_dantzig_static: set actions (or None), n dense-solver sub-steps on the library's static scratch, bodies out
+        (or None) -- the call that allocates nothing; n_envs <= abi.NOALLOC_MAX_ENVS."""
+        a = _dp(actions_dev) if actions_dev is not None else None
+        o = _dp(bodies_out_dev) if bodies_out_dev is not None else None
+        self._ck(self.L.tfode_batch_step_dantzig_static(self.h, a, int(n_substeps), o))
 
     def lcp_failures(self):
         n = C.c_int64(0)
