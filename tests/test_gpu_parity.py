@@ -206,7 +206,9 @@ def numpy_mlp_bf16(w, x):
 
 @pytest.mark.parametrize("m", [1, 7, 128, 129, 1000, 16384])
 def test_policy_tc_matches_bf16_reference(m):
-    """tcgen05 kernel vs numpy with the same operand rounding: only the fp32 accumulation order differs (<= 2e-4);
+    """tcgen05 kernel vs numpy with the same operand rounding: the fp32 accumulation order differs (the kernel walks K in a rotated
+    order per CTA and adds the biases inside the accumulation), and a hidden activation that lands within an fp32 ulp of a bf16 rounding
+    boundary may round the other way (one bf16 ulp of one of 512 activations): <= 5e-4 on a tanh output;
     vs the fp64 MLP on unrounded weights the bf16 operands cost <= 3e-2 on a tanh output (stated tolerance of the
     TFODE_POLICY_TC path; the fp32 kernel stays the bit-exact parity path)."""
     g = RoverBatch(make_config(abi.PRESET_TRAINING, 8, policy_precision=abi.POLICY_TC))
@@ -222,7 +224,7 @@ def test_policy_tc_matches_bf16_reference(m):
     g.policy_infer(torch.from_numpy(x).cuda(), yd)
     torch.cuda.synchronize()
     y = yd.cpu().numpy()
-    assert np.abs(y - numpy_mlp_bf16(w, x)).max() <= 2e-4
+    assert np.abs(y - numpy_mlp_bf16(w, x)).max() <= 5e-4
     assert np.abs(y - numpy_mlp(w, x)).max() <= 3e-2
     g.close()
 

@@ -1,21 +1,25 @@
 // tcgen05 policy path (TFODE_POLICY_TC): TF_model<float>::infer (tf_cpp_binding.cc:70-113) for the actor of
 // scripts/rover_training_1.py:26-35 (17 -> 512 relu -> 512 relu -> 2 tanh) on the 5th-generation tensor cores.
 //
-// One CTA = 128 environments (the M of a 128xNx16 UMMA tile = the 128 TMEM lanes).  Per CTA:
-//   gather  : thread r gathers its environment's 17 scaled observations (parked list or direct rows), rounds them to
-//             bf16 and stores them as the A operand (K padded to 32) in the UMMA canonical K-major no-swizzle layout
-//   layer 1 : W1 (bf16, canonical, 32 KB) arrives by one bulk TMA copy; 4 x tcgen05.mma (N=256 halves x 2 K-steps)
-//             accumulate H1[128][512] in fp32 into all 512 TMEM columns
-//   epilogue: every thread reads its lane's 512 columns with tcgen05.ld, adds b1, ReLU, rounds to bf16 and writes the
-//             layer-2 A operand (128 KB) straight back into shared memory in the canonical layout
-//   layer 2 : W2 (512 KB) streams through a 2-stage 32 KB ring of bulk TMA copies tracked by mbarriers; 64 x
-//             tcgen05.mma into the same TMEM columns; tcgen05.commit releases ring slots and signals the epilogue
-//   epilogue: b2 + ReLU in fp32, the 512 -> 2 output layer as two fp32 dot products per thread, tanh, and the two
-//             actions go straight into the environment record (policy_act, parked = 2) that the step kernel turns
-//             into the steering-rate / boggie-torque setpoints (src/rover_1_tf.cc:184-185).
+// One CTA = 128 environments (the M of a 128xNx16 UMMA tile = the 128 TMEM lanes), ten warps in three roles:
+//   warp 8 (one lane)  producer: W1 (32 KB, one bulk TMA copy) and then W2 as 32 slabs of 16 KB (K = 32 x N = 256, one N half after the
+//                      other) through a 5-slot ring tracked by full/empty mbarriers -- it starts at kernel entry, so the stream from L2 runs
+//                      under the gather, layer 1 and its epilogue and never waits for anything but a free slot
+//   warp 9 (one lane)  MMA issuer (and TMEM owner): 4 x tcgen05.mma for layer 1 (all 512 TMEM columns), then 2 per slab for layer 2;
+//                      tcgen05.commit frees ring slots and signals "N half 0 done" / "N half 1 done"
+//   warps 0-7          gather + epilogues; warp w reads TMEM lanes 32 (w % 4) .., the two warps of a lane quarter split the columns
+//     gather    : thread r < 128 rounds its environment's 17 scaled observations (parked list or direct rows) to bf16 and stores them as the
+//                 layer-1 A operand (K padded to 32) in the UMMA canonical K-major no-swizzle layout
+//     epilogue 1: tcgen05.ld, + b1, ReLU, bf16, written straight back to shared memory as the layer-2 A operand (128 KB, canonical layout;
+//                 W1 and the layer-1 A operand lived in the same bytes)
+//     epilogue 2: N half 0 (columns 0-255) is reduced while the tensor core works on N half 1: + b2, ReLU in fp32, the 512 -> 2 output
+//                 layer as two fp32 dot products per thread; then half 1, tanh, and the two actions go straight into the environment
+//                 record (policy_act, parked = 2) that the step kernel turns into the steering-rate / boggie-torque setpoints
+//                 (src/rover_1_tf.cc:184-185).
 // Operand layout (bf16, "core matrix" = 8 rows x 16 bytes, stored as 128 contiguous bytes):
 //   element (row, k) of an operand with R rows lives at  (k/8) * (R/8)*128 + (row/8)*128 + (row%8)*16 + (k%8)*2
 //   => stride-dimension byte offset (next 8 rows) = 128, leading-dimension byte offset (next 8 k) = R*16.
+// W2 in global memory is stored slab by slab ([N half][K slab of 32] -> a canonical operand with R = 256 rows), so a slab is 16 KB contiguous.
 #pragma once
 #include <cuda_bf16.h>
 
@@ -26,27 +30,36 @@
 namespace tfode {
 
 constexpr int TC_ROWS = 128;                   // environments per CTA
+constexpr int TC_THREADS = 320;                // 8 epilogue warps + producer + MMA issuer
 constexpr int TC_H = TFODE_MLP_HIDDEN;         // 512
 constexpr int TC_K1 = 32;                      // 17 padded to two K=16 steps
 constexpr int TC_SLAB_K = 32;                  // K extent of one W2 ring slot
-constexpr int TC_SLAB_BYTES = TC_H * TC_SLAB_K * 2;   // 32 KB
-constexpr int TC_NSLAB = TC_H / TC_SLAB_K;     // 16
+constexpr int TC_SLAB_N = 256;                 // N extent of one W2 ring slot (one MMA's N)
+constexpr int TC_SLAB_BYTES = TC_SLAB_N * TC_SLAB_K * 2;      // 16 KB
+constexpr int TC_NSLAB = (TC_H / TC_SLAB_K) * (TC_H / TC_SLAB_N);   // 32: slabs 0-15 are N half 0, 16-31 N half 1
+#ifndef TFODE_TC_NSLOT
+#define TFODE_TC_NSLOT 5
+#endif
+constexpr int TC_NSLOT = TFODE_TC_NSLOT;
+constexpr int TC_W1_BYTES = TC_H * TC_K1 * 2;         // 32 KB
 constexpr int TC_A2_BYTES = TC_ROWS * TC_H * 2;       // 128 KB
 constexpr int TC_A1_BYTES = TC_ROWS * TC_K1 * 2;      // 8 KB
 // shared memory map (bytes)
-constexpr int TC_OFF_A2 = 0;
-constexpr int TC_OFF_RING = TC_OFF_A2 + TC_A2_BYTES;            // 2 slots; slot 0 first holds W1
-constexpr int TC_OFF_A1 = TC_OFF_RING + 2 * TC_SLAB_BYTES;
-constexpr int TC_OFF_B1 = TC_OFF_A1 + TC_A1_BYTES;              // fp32 b1[512]
-constexpr int TC_OFF_B2 = TC_OFF_B1 + TC_H * 4;                 // fp32 b2[512]
-constexpr int TC_OFF_W3 = TC_OFF_B2 + TC_H * 4;                 // fp32 W3[512][2]
-constexpr int TC_OFF_BAR = TC_OFF_W3 + TC_H * 2 * 4;            // mbarriers: full[2], empty[2], done
-constexpr int TC_OFF_TMEM = TC_OFF_BAR + 8 * 8;
+constexpr int TC_OFF_A2 = 0;                                    // layer-2 A operand; before epilogue 1: W1 at +0, layer-1 A operand at +32 KB
+constexpr int TC_OFF_W1 = TC_OFF_A2;
+constexpr int TC_OFF_A1 = TC_OFF_W1 + TC_W1_BYTES;
+constexpr int TC_OFF_RING = TC_OFF_A2 + TC_A2_BYTES;            // 5 slots of 16 KB
+constexpr int TC_OFF_B2 = TC_OFF_RING + TC_NSLOT * TC_SLAB_BYTES;   // fp32 b2[512]
+constexpr int TC_OFF_W3 = TC_OFF_B2 + TC_H * 4;                 // fp32 W3 transposed: [2][512]
+constexpr int TC_OFF_PART = TC_OFF_W3 + TC_H * 2 * 4;           // fp32 partial output sums [128][2]
+constexpr int TC_OFF_BAR = TC_OFF_PART + TC_ROWS * 2 * 4;       // mbarriers: full[5], empty[5], W1, A1, L1, A2, H0, H1
+constexpr int TC_OFF_TMEM = TC_OFF_BAR + 16 * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
+static_assert(TC_A1_BYTES + TC_W1_BYTES <= TC_A2_BYTES && TC_SMEM_BYTES <= 227 * 1024, "shared memory map");
 
 struct PolicyTC {
   __nv_bfloat16* w1c = nullptr;  // [4 k-cores][64 n-cores][8][8]
-  __nv_bfloat16* w2c = nullptr;  // [64 k-cores][64 n-cores][8][8]
+  __nv_bfloat16* w2c = nullptr;  // [2 N halves][16 K slabs][4 k-cores][32 n-cores][8][8]
   bool attr_set = false;
 };
 
@@ -60,6 +73,10 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }   // the eight gather / epilogue warps
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -68,6 +85,24 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "@p bra DONE_%=;\n\t"
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+// Developer experiment (TFODE_TC_EXP_SLEEPY): a whole warp waits, one lane polls with a suspend-time hint instead of every thread re-reading
+// the barrier word in a tight loop.
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+#ifdef TFODE_TC_EXP_SLEEPY   // measured: wakes ~150 clk later than the plain poll and the MMAs run no faster -- polling is not what slows them
+  if ((threadIdx.x & 31) == 0) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAITW_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
+        "@p bra DONEW_%=;\n\t"
+        "bra WAITW_%=;\n\t"
+        "DONEW_%=:\n\t}" ::"r"(bar), "r"(parity), "r"(20000u) : "memory");
+  }
+  __syncwarp();
+#else
+  mbar_wait(bar, parity);
+#endif
 }
 // 1-D bulk TMA copy global -> shared, completion counted in bytes on an mbarrier
 __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
@@ -94,7 +129,7 @@ __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = lane)
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -104,7 +139,47 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr)
       : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// tcgen05.wait::ld, written so that every use of v[] depends on it (the registers are only valid after the wait)
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.wait::ld.sync.aligned;"
+      : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]),
+        "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]),
+        "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+      :
+      : "memory");
+}
+// 32 registers per thread -> 32 lanes x 32 consecutive fp32 columns
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      :
+      : "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+        "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+        "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// ReLU + round to bf16 + pack in one instruction: low half = relu(lo), high half = relu(hi)
+__device__ __forceinline__ uint32_t pack_relu_bf16(uint32_t lo, uint32_t hi) {
+  uint32_t d;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(__uint_as_float(hi)), "f"(__uint_as_float(lo)));
+  return d;
+}
+// packed fp32 pair arithmetic (sm_100): acc.{lo,hi} += a.{lo,hi} * w.{lo,hi}
+__device__ __forceinline__ uint64_t pack_f32x2(float lo, float hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(lo), "f"(hi));
+  return d;
+}
+__device__ __forceinline__ void fma_f32x2(uint64_t& acc, uint64_t a, uint64_t w) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(w)); }
+__device__ __forceinline__ float sum_f32x2(uint64_t v) {
+  float lo, hi;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+  return lo + hi;
 }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);  // .x = lo (low half), .y = hi
@@ -113,8 +188,19 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 
 }  // namespace tc
 
+// Developer timeline (tools/policy_tc_timeline.cu builds with -DTFODE_TC_TIMELINE): clock64 at the role hand-overs of every CTA
+#ifdef TFODE_TC_TIMELINE
+__device__ long long g_tc_timeline[2048 * 16];
+__device__ long long g_tc_slabs[64 * 4];   // CTA 0: per slab {TMA issued, full-wait begins, full-wait ends, MMAs issued}
+#define TC_MARK(i) (g_tc_timeline[(blockIdx.x & 2047) * 16 + (i)] = clock64())
+#define TC_SLAB_MARK(s, j) do { if (blockIdx.x == 0) g_tc_slabs[(s) * 4 + (j)] = clock64(); } while (0)
+#else
+#define TC_MARK(i) ((void)0)
+#define TC_SLAB_MARK(s, j) ((void)0)
+#endif
+
 // in_all: [*,17] scaled observations; list/n_list: parked environments (device) or nullptr for direct rows [0, m_direct)
-__global__ void __launch_bounds__(TC_ROWS, 1)
+__global__ void __launch_bounds__(TC_THREADS, 1)
 policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list, const int* __restrict__ n_list, int m_direct,
                  const __nv_bfloat16* __restrict__ w1c, const __nv_bfloat16* __restrict__ w2c, const float* __restrict__ b1,
                  const float* __restrict__ b2, const float* __restrict__ W3, const float* __restrict__ b3, EnvRec* rec, float* act_direct) {
@@ -123,146 +209,207 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
   const int m = list ? *n_list : m_direct;
   const int row0 = blockIdx.x * TC_ROWS;
   if (row0 >= m) return;                       // uniform per CTA, before any allocation
-  const int t = threadIdx.x, warp = t >> 5;
-  const int row = row0 + t;
-  const bool valid = row < m;
-  const int src = valid ? (list ? list[row] : row) : -1;
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  if (t == 0) TC_MARK(0);
 
-  const uint32_t sA2 = smem_u32(smem + TC_OFF_A2), sRing = smem_u32(smem + TC_OFF_RING), sA1 = smem_u32(smem + TC_OFF_A1);
-  const uint32_t barFull0 = smem_u32(smem + TC_OFF_BAR), barEmpty0 = barFull0 + 16, barDone = barFull0 + 32;
-  float* sb1 = reinterpret_cast<float*>(smem + TC_OFF_B1);
+  const uint32_t sA2 = smem_u32(smem + TC_OFF_A2), sRing = smem_u32(smem + TC_OFF_RING), sA1 = smem_u32(smem + TC_OFF_A1), sW1 = smem_u32(smem + TC_OFF_W1);
+  const uint32_t barFull = smem_u32(smem + TC_OFF_BAR), barEmpty = barFull + 8 * TC_NSLOT, barW1 = barFull + 80, barA1 = barFull + 88, barL1 = barFull + 96,
+                 barA2 = barFull + 104, barH0 = barFull + 112, barH1 = barFull + 120;
   float* sb2 = reinterpret_cast<float*>(smem + TC_OFF_B2);
   float* sW3 = reinterpret_cast<float*>(smem + TC_OFF_W3);
+  float* sPart = reinterpret_cast<float*>(smem + TC_OFF_PART);
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + TC_OFF_TMEM);
 
   if (t == 0) {
-    mbar_init(barFull0, 1); mbar_init(barFull0 + 8, 1);
-    mbar_init(barEmpty0, 1); mbar_init(barEmpty0 + 8, 1);
-    mbar_init(barDone, 1);
+    for (int i = 0; i < TC_NSLOT; i++) { mbar_init(barFull + 8 * i, 1); mbar_init(barEmpty + 8 * i, 1); }
+    mbar_init(barW1, 1); mbar_init(barA1, TC_ROWS); mbar_init(barL1, 1); mbar_init(barA2, 256); mbar_init(barH0, 1); mbar_init(barH1, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    // W1 into ring slot 0 while the rows are gathered
-    mbar_expect_tx(barFull0, TC_SLAB_BYTES);
-    tma_bulk_g2s(sRing, w1c, TC_SLAB_BYTES, barFull0);
   }
-  if (warp == 1) {  // one warp owns the TMEM allocation (all 512 columns: 128 lanes x 512 fp32 accumulators)
+  if (warp == 9) {  // one warp owns the TMEM allocation (all 512 columns: 128 lanes x 512 fp32 accumulators)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem + TC_OFF_TMEM)), "r"(512) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // biases and the output layer, fp32
-  for (int i = t; i < TC_H; i += TC_ROWS) { sb1[i] = b1[i]; sb2[i] = b2[i]; sW3[2 * i] = W3[2 * i]; sW3[2 * i + 1] = W3[2 * i + 1]; }
-  // A1: this thread's row, K = 32 (17 observations, zero padded), 4 k-cores of 16 bytes
-  {
-    float x[TC_K1];
-#pragma unroll
-    for (int k = 0; k < TC_K1; k++) x[k] = (valid && k < 17) ? in_all[(size_t)src * 17 + k] : 0.0f;
-#pragma unroll
-    for (int kc = 0; kc < TC_K1 / 8; kc++) {
-      uint4 q = make_uint4(pack_bf16(x[kc * 8], x[kc * 8 + 1]), pack_bf16(x[kc * 8 + 2], x[kc * 8 + 3]), pack_bf16(x[kc * 8 + 4], x[kc * 8 + 5]),
-                           pack_bf16(x[kc * 8 + 6], x[kc * 8 + 7]));
-      *reinterpret_cast<uint4*>(smem + TC_OFF_A1 + kc * (TC_ROWS * 16) + t * 16) = q;
-    }
-  }
-  fence_proxy_async();     // generic-proxy stores of A1 must be visible to the tensor core (async proxy)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  if (t == 0) TC_MARK(1);
+  // The CTAs of a launch run in step and W2 is the same 512 KB for all of them: started on the same slab they would all pull the same
+  // 16 KB out of the same few L2 slices at the same moment (measured: 30 B/clk per SM).  Each CTA therefore walks the 16 K slabs of an
+  // N half from its own offset; the sum over K is the same set of products, accumulated in a rotated order.
+  const int k0 = blockIdx.x & 15;
 
-  // ---- layer 1: H1 = X(128x32) . W1^T, N in two halves of 256 columns
-  if (t == 0) {
-    mbar_wait(barFull0, 0);
-    tc_fence_after();
-#pragma unroll
-    for (int ks = 0; ks < TC_K1 / 16; ks++)
-#pragma unroll
-      for (int h = 0; h < 2; h++) {
-        const uint64_t ad = make_desc(sA1 + ks * 2 * (TC_ROWS * 16), TC_ROWS * 16, 128);
-        const uint64_t bd = make_desc(sRing + ks * 2 * (TC_H * 16) + h * (256 / 8) * 128, TC_H * 16, 128);
-        mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, ks > 0);
+  if (warp == 8) {
+    // ---- producer: W1, then the 32 W2 slabs through the ring
+    if (lane == 0) {
+      mbar_expect_tx(barW1, TC_W1_BYTES);
+      tma_bulk_g2s(sW1, w1c, TC_W1_BYTES, barW1);
+#pragma unroll 1
+      for (int s = 0; s < TC_NSLAB; s++) {
+        const int slot = s % TC_NSLOT, round = s / TC_NSLOT;
+        if (round > 0) mbar_wait(barEmpty + 8 * slot, (uint32_t)(round - 1) & 1u);
+        mbar_expect_tx(barFull + 8 * slot, TC_SLAB_BYTES);
+        const int gslab = (s & 16) | ((s + k0) & 15);   // N half, rotated K slab
+        TC_SLAB_MARK(s, 0);
+        tma_bulk_g2s(sRing + slot * TC_SLAB_BYTES, reinterpret_cast<const uint8_t*>(w2c) + (size_t)gslab * TC_SLAB_BYTES, TC_SLAB_BYTES, barFull + 8 * slot);
       }
-    mma_commit(barDone);
-  }
-  mbar_wait(barDone, 0);
-  tc_fence_after();
-  if (t == 0) {  // ring slot 0 (W1) is free again: start streaming W2 slabs 0 and 1 under the epilogue
-    mbar_expect_tx(barFull0, TC_SLAB_BYTES);
-    tma_bulk_g2s(sRing, w2c, TC_SLAB_BYTES, barFull0);
-    mbar_expect_tx(barFull0 + 8, TC_SLAB_BYTES);
-    tma_bulk_g2s(sRing + TC_SLAB_BYTES, reinterpret_cast<const uint8_t*>(w2c) + TC_SLAB_BYTES, TC_SLAB_BYTES, barFull0 + 8);
-  }
-  // ---- epilogue 1: bias + ReLU + bf16, written as the layer-2 A operand
-  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
-#pragma unroll 1
-  for (int c = 0; c < TC_H / 32; c++) {
-    uint32_t v[32];
-    tmem_ld32(lane_base + c * 32, v);
-#pragma unroll
-    for (int g = 0; g < 4; g++) {
-      float f[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) { float a = __uint_as_float(v[g * 8 + i]) + sb1[c * 32 + g * 8 + i]; f[i] = a > 0.0f ? a : 0.0f; }
-      uint4 q = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-      *reinterpret_cast<uint4*>(smem + TC_OFF_A2 + (c * 4 + g) * (TC_ROWS * 16) + t * 16) = q;
+      TC_MARK(11);
     }
-  }
-  fence_proxy_async();
-  tc_fence_before();       // the tcgen05.ld reads of H1 are ordered before the MMAs that overwrite those columns
-  __syncthreads();
-  tc_fence_after();
-
-  // ---- layer 2: H2 = relu(H1)(128x512) . W2^T, W2 streamed in 16 slabs of K = 32 through the 2-slot ring
-  if (t == 0) {
-#pragma unroll 1
-    for (int s = 0; s < TC_NSLAB; s++) {
-      const int slot = s & 1;
-      const uint32_t ph = (uint32_t)(s >> 1) & 1u;
-      // full[slot] completed once already for slot 0 (W1): its phase for W2 slab s is shifted by one
-      mbar_wait(barFull0 + 8 * slot, slot == 0 ? (ph ^ 1u) : ph);
+  } else if (warp == 9) {
+    // ---- MMA issuer
+    if (lane == 0) {
+      mbar_wait(barW1, 0);
+      mbar_wait(barA1, 0);
       tc_fence_after();
+      TC_MARK(2);
+      // layer 1: H1 = X(128x32) . W1^T, N in two halves of 256 columns
 #pragma unroll
-      for (int ks = 0; ks < TC_SLAB_K / 16; ks++)
+      for (int ks = 0; ks < TC_K1 / 16; ks++)
 #pragma unroll
         for (int h = 0; h < 2; h++) {
-          const uint64_t ad = make_desc(sA2 + (s * (TC_SLAB_K / 8) + ks * 2) * (TC_ROWS * 16), TC_ROWS * 16, 128);
-          const uint64_t bd = make_desc(sRing + slot * TC_SLAB_BYTES + ks * 2 * (TC_H * 16) + h * (256 / 8) * 128, TC_H * 16, 128);
-          mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, (s | ks) > 0);
+          const uint64_t ad = make_desc(sA1 + ks * 2 * (TC_ROWS * 16), TC_ROWS * 16, 128);
+          const uint64_t bd = make_desc(sW1 + ks * 2 * (TC_H * 16) + h * (256 / 8) * 128, TC_H * 16, 128);
+          mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, ks > 0);
         }
-      mma_commit(barEmpty0 + 8 * slot);       // arrives when the MMAs above have finished reading the slot
-      // refill the OTHER slot (slab s-1's) with slab s+1 while slab s is in the tensor pipe
-      if (s >= 1 && s + 1 < TC_NSLAB) {
-        const int oslot = slot ^ 1;
-        mbar_wait(barEmpty0 + 8 * oslot, (uint32_t)((s - 1) >> 1) & 1u);
-        mbar_expect_tx(barFull0 + 8 * oslot, TC_SLAB_BYTES);
-        tma_bulk_g2s(sRing + oslot * TC_SLAB_BYTES, reinterpret_cast<const uint8_t*>(w2c) + (size_t)(s + 1) * TC_SLAB_BYTES, TC_SLAB_BYTES, barFull0 + 8 * oslot);
+      mma_commit(barL1);
+      // layer 2: H2 = relu(H1)(128x512) . W2^T; N half 0 over all of K, then N half 1
+      mbar_wait(barA2, 0);
+      tc_fence_after();
+      TC_MARK(3);
+#pragma unroll 1
+      for (int s = 0; s < TC_NSLAB; s++) {
+        const int slot = s % TC_NSLOT, round = s / TC_NSLOT;
+        const int h = s >> 4, kslab = (s + k0) & 15;
+        TC_SLAB_MARK(s, 1);
+#ifndef TFODE_TC_EXP_NOWAIT   // developer experiment: raw MMA issue rate, operands = whatever the ring holds
+        mbar_wait(barFull + 8 * slot, (uint32_t)round & 1u);
+#endif
+        TC_SLAB_MARK(s, 2);
+#ifndef TFODE_TC_EXP_NOFENCE
+        tc_fence_after();
+#endif
+        if (s == 0) TC_MARK(13);
+        if (s == TC_NSLAB / 2 - 1) TC_MARK(12);
+        if (s == TC_NSLAB - 1) TC_MARK(4);
+#pragma unroll
+        for (int ks = 0; ks < TC_SLAB_K / 16; ks++) {
+#ifdef TFODE_TC_EXP_LAYOUT   // developer experiment (with TFODE_TC_EXP_NOWAIT; results are garbage): raw MMA rate with a swizzled operand layout type
+          const uint64_t ad = (make_desc(sA2 + (kslab & 7) * 16384 + ks * 32, 16, 1024) & ~(7ull << 61)) | ((uint64_t)TFODE_TC_EXP_LAYOUT << 61);
+          const uint64_t bd = (make_desc(sRing + ks * 32, 16, 1024) & ~(7ull << 61)) | ((uint64_t)TFODE_TC_EXP_LAYOUT << 61);
+#else
+          const uint64_t ad = make_desc(sA2 + (kslab * (TC_SLAB_K / 8) + ks * 2) * (TC_ROWS * 16), TC_ROWS * 16, 128);
+          const uint64_t bd = make_desc(sRing + slot * TC_SLAB_BYTES + ks * 2 * (TC_SLAB_N * 16), TC_SLAB_N * 16, 128);
+#endif
+          mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, 1u);   // the accumulators start from b2 (epilogue 1 put it there)
+        }
+        mma_commit(barEmpty + 8 * slot);       // arrives when the MMAs above have finished reading the slot
+        TC_SLAB_MARK(s, 3);
+        if (s == TC_NSLAB / 2 - 1) mma_commit(barH0);
+      }
+      mma_commit(barH1);
+    }
+  } else {
+    // ---- gather and epilogues: lane quarter q = TMEM lanes 32 q .., column group g
+    const int q = warp & 3, g = warp >> 2;
+    const int r = q * 32 + lane;               // row of the tile this thread owns in TMEM
+    const int row = row0 + r;
+    const bool valid = row < m;
+    const int src = valid ? (list ? list[row] : row) : -1;
+    if (t < TC_ROWS) {
+      // A1: row t, K = 32 (17 observations, zero padded), 4 k-cores of 16 bytes  (t == r for warps 0-3)
+      float x[TC_K1];
+#pragma unroll
+      for (int k = 0; k < TC_K1; k++) x[k] = (valid && k < 17) ? in_all[(size_t)src * 17 + k] : ((k == 17 || k == 18) ? 1.0f : 0.0f);   // k = 17, 18 multiply the two bf16 pieces of b1
+#pragma unroll
+      for (int kc = 0; kc < TC_K1 / 8; kc++) {
+        uint4 qv = make_uint4(pack_bf16(x[kc * 8], x[kc * 8 + 1]), pack_bf16(x[kc * 8 + 2], x[kc * 8 + 3]), pack_bf16(x[kc * 8 + 4], x[kc * 8 + 5]),
+                              pack_bf16(x[kc * 8 + 6], x[kc * 8 + 7]));
+        *reinterpret_cast<uint4*>(smem + TC_OFF_A1 + kc * (TC_ROWS * 16) + t * 16) = qv;
+      }
+      fence_proxy_async();     // generic-proxy stores of A1 must be visible to the tensor core (async proxy)
+      mbar_arrive(barA1);
+    } else {
+      // biases and the output layer, fp32
+      for (int i = t - TC_ROWS; i < TC_H; i += TC_ROWS) { sb2[i] = b2[i]; sW3[i] = W3[2 * i]; sW3[TC_H + i] = W3[2 * i + 1]; }
+    }
+    epi_bar_sync();
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
+
+    // ---- epilogue 1: ReLU + bf16 (b1 came in through the MMA), written as the layer-2 A operand; group g takes columns [256 g, 256 g + 256)
+    mbar_wait_warp(barL1, 0);
+    tc_fence_after();
+    if (t == 0) TC_MARK(5);
+#pragma unroll 1
+    for (int ci = 0; ci < 8; ci += 2) {          // two chunks of 32 columns in flight per round trip to TMEM
+      const int c = g * 8 + ci;
+      uint32_t v[2][32], bias[2][32];
+      tmem_ld32_issue(lane_base + c * 32, v[0]);
+      tmem_ld32_issue(lane_base + c * 32 + 32, v[1]);
+#pragma unroll
+      for (int u = 0; u < 2; u++)
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const uint4 bb = *reinterpret_cast<const uint4*>(sb2 + (c + u) * 32 + i);
+          bias[u][i] = bb.x; bias[u][i + 1] = bb.y; bias[u][i + 2] = bb.z; bias[u][i + 3] = bb.w;
+        }
+      tmem_ld_wait(v[0]); tmem_ld_wait(v[1]);
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+#pragma unroll
+        for (int gg = 0; gg < 4; gg++) {
+          uint4 qv = make_uint4(pack_relu_bf16(v[u][gg * 8], v[u][gg * 8 + 1]), pack_relu_bf16(v[u][gg * 8 + 2], v[u][gg * 8 + 3]),
+                                pack_relu_bf16(v[u][gg * 8 + 4], v[u][gg * 8 + 5]), pack_relu_bf16(v[u][gg * 8 + 6], v[u][gg * 8 + 7]));
+          *reinterpret_cast<uint4*>(smem + TC_OFF_A2 + ((c + u) * 4 + gg) * (TC_ROWS * 16) + r * 16) = qv;
+        }
+        tmem_st32(lane_base + (c + u) * 32, bias[u]);   // these 32 columns are read: they become layer-2 accumulators and start from b2
       }
     }
-    mma_commit(barDone);
-  }
-  mbar_wait(barDone, 1);
-  tc_fence_after();
+    tmem_wait_st();
+    fence_proxy_async();
+    tc_fence_before();       // the tcgen05.ld reads of H1 are ordered before the MMAs that overwrite those columns
+    mbar_arrive(barA2);
+    if (t == 0) TC_MARK(6);
 
-  // ---- epilogue 2: bias + ReLU, output layer 512 -> 2 in fp32, tanh, actions into the environment record
-  float s0 = 0.0f, s1 = 0.0f;
+    // ---- epilogue 2: ReLU (b2 was the accumulators' start value), output layer 512 -> 2 in fp32; N half 0 while half 1 is in the tensor pipe, group g takes 128 columns of each
+    uint64_t acc0 = 0ull, acc1 = 0ull;   // (even columns, odd columns) partial sums of output 0 / output 1
 #pragma unroll 1
-  for (int c = 0; c < TC_H / 32; c++) {
-    uint32_t v[32];
-    tmem_ld32(lane_base + c * 32, v);
+    for (int half = 0; half < 2; half++) {
+      mbar_wait_warp(half ? barH1 : barH0, 0);
+      tc_fence_after();
+      if (t == 0) TC_MARK(half ? 9 : 7);
+      const int c0 = half * 8 + g * 4;
+      uint32_t v[4][32];
 #pragma unroll
-    for (int i = 0; i < 32; i++) {
-      float a = __uint_as_float(v[i]) + sb2[c * 32 + i];
-      a = a > 0.0f ? a : 0.0f;
-      s0 = fmaf(a, sW3[2 * (c * 32 + i)], s0);
-      s1 = fmaf(a, sW3[2 * (c * 32 + i) + 1], s1);
+      for (int ci = 0; ci < 4; ci++) tmem_ld32_issue(lane_base + (c0 + ci) * 32, v[ci]);
+#pragma unroll
+      for (int ci = 0; ci < 4; ci++) tmem_ld_wait(v[ci]);
+#pragma unroll
+      for (int ci = 0; ci < 4; ci++) {
+        const int c = c0 + ci;
+#pragma unroll
+        for (int i = 0; i < 32; i += 4) {
+          const ulonglong2 w0 = *reinterpret_cast<const ulonglong2*>(sW3 + c * 32 + i), w1 = *reinterpret_cast<const ulonglong2*>(sW3 + TC_H + c * 32 + i);
+          const uint64_t a01 = pack_f32x2(fmaxf(__uint_as_float(v[ci][i]), 0.0f), fmaxf(__uint_as_float(v[ci][i + 1]), 0.0f));
+          const uint64_t a23 = pack_f32x2(fmaxf(__uint_as_float(v[ci][i + 2]), 0.0f), fmaxf(__uint_as_float(v[ci][i + 3]), 0.0f));
+          fma_f32x2(acc0, a01, w0.x); fma_f32x2(acc1, a01, w1.x);
+          fma_f32x2(acc0, a23, w0.y); fma_f32x2(acc1, a23, w1.y);
+        }
+      }
     }
-  }
-  if (valid) {
-    const float a0 = tfn::tanh(s0 + b3[0]), a1 = tfn::tanh(s1 + b3[1]);
-    if (list) { EnvRec& e = rec[src]; e.c.policy_act[0] = a0; e.c.policy_act[1] = a1; e.c.parked = 2; }
-    else { act_direct[(size_t)row * 2] = a0; act_direct[(size_t)row * 2 + 1] = a1; }
+    const float s0 = sum_f32x2(acc0), s1 = sum_f32x2(acc1);
+    if (t == 0) TC_MARK(8);
+    if (g == 1) { sPart[2 * r] = s0; sPart[2 * r + 1] = s1; }
+    epi_bar_sync();
+    if (g == 0 && valid) {
+      const float a0 = tfn::tanh(s0 + sPart[2 * r] + b3[0]), a1 = tfn::tanh(s1 + sPart[2 * r + 1] + b3[1]);
+      if (list) { EnvRec& e = rec[src]; e.c.policy_act[0] = a0; e.c.policy_act[1] = a1; e.c.parked = 2; }
+      else { act_direct[(size_t)row * 2] = a0; act_direct[(size_t)row * 2 + 1] = a1; }
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
+  if (t == 0) TC_MARK(10);
+  if (warp == 9) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512) : "memory");
 }
 
 // ---- host side: operand preparation and launch ----
@@ -280,12 +427,32 @@ inline void tc_pack_operand(const float* W, int k_in, int kpad, std::vector<uint
     for (int n = 0; n < TC_H; n++)
       out[(size_t)(k / 8) * (TC_H / 8) * 64 + (size_t)(n / 8) * 64 + (n % 8) * 8 + (k % 8)] = tc_bf16_rn(W[(size_t)k * TC_H + n]);
 }
+// W2 for the ring: [N half h][K slab of 32] -> one canonical operand of R = 256 rows (n) x 32 k, 16 KB contiguous per slab
+inline void tc_pack_w2_slabs(const float* W, std::vector<uint16_t>& out) {
+  out.assign((size_t)TC_H * TC_H, 0);
+  for (int k = 0; k < TC_H; k++)
+    for (int n = 0; n < TC_H; n++) {
+      const int h = n / TC_SLAB_N, nl = n % TC_SLAB_N, slab = k / TC_SLAB_K, kl = k % TC_SLAB_K;
+      const size_t base = (size_t)(h * (TC_H / TC_SLAB_K) + slab) * (TC_SLAB_BYTES / 2);
+      out[base + (size_t)(kl / 8) * (TC_SLAB_N / 8) * 64 + (size_t)(nl / 8) * 64 + (nl % 8) * 8 + (kl % 8)] = tc_bf16_rn(W[(size_t)k * TC_H + n]);
+    }
+}
 inline int policy_tc_upload(PolicyTC& tcw, const float* w_host, cudaStream_t stream) {
   const size_t H = TC_H;
   const float* W1 = w_host; const float* W2 = w_host + 17 * H + H;
   std::vector<uint16_t> p1, p2;
   tc_pack_operand(W1, 17, TC_K1, p1);
-  tc_pack_operand(W2, TC_H, TC_H, p2);
+  {  // b1 rides in the K padding of layer 1 as two bf16 pieces (hi + lo: 2^-17 relative), multiplied by the ones the gather puts at k = 17, 18
+    const float* b1 = w_host + 17 * H;
+    for (int n = 0; n < TC_H; n++) {
+      const uint16_t hi = tc_bf16_rn(b1[n]);
+      uint32_t u = (uint32_t)hi << 16; float fhi; memcpy(&fhi, &u, 4);
+      const uint16_t lo = tc_bf16_rn(b1[n] - fhi);
+      const uint16_t piece[2] = {hi, lo};
+      for (int j = 0; j < 2; j++) { const int k = 17 + j; p1[(size_t)(k / 8) * (TC_H / 8) * 64 + (size_t)(n / 8) * 64 + (n % 8) * 8 + (k % 8)] = piece[j]; }
+    }
+  }
+  tc_pack_w2_slabs(W2, p2);
   if (!tcw.w1c && cudaMalloc(&tcw.w1c, p1.size() * 2) != cudaSuccess) return -1;
   if (!tcw.w2c && cudaMalloc(&tcw.w2c, p2.size() * 2) != cudaSuccess) return -1;
   if (cudaMemcpyAsync(tcw.w1c, p1.data(), p1.size() * 2, cudaMemcpyHostToDevice, stream) != cudaSuccess) return -1;
@@ -304,7 +471,7 @@ inline cudaError_t policy_tc_launch(PolicyTC& tcw, const float* in, const int* l
     tcw.attr_set = true;
   }
   const int blocks = (max_rows + TC_ROWS - 1) / TC_ROWS;
-  policy_tc_kernel<<<blocks, TC_ROWS, TC_SMEM_BYTES, stream>>>(in, list, n_list, m_direct, tcw.w1c, tcw.w2c, b1, b2, W3, b3, rec, act_direct);
+  policy_tc_kernel<<<blocks, TC_THREADS, TC_SMEM_BYTES, stream>>>(in, list, n_list, m_direct, tcw.w1c, tcw.w2c, b1, b2, W3, b3, rec, act_direct);
   return cudaGetLastError();
 }
 }  // namespace tfode
