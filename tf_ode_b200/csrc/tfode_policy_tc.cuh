@@ -2,20 +2,30 @@
 // scripts/rover_training_1.py:26-35 (17 -> 512 relu -> 512 relu -> 2 tanh) on the 5th-generation tensor cores.
 //
 // One CTA = 128 environments (the M of a 128xNx16 UMMA tile = the 128 TMEM lanes), ten warps in three roles:
-//   warp 8 (one lane)  producer: W1 (32 KB, one bulk TMA copy) and then W2 as 32 slabs of 16 KB (K = 32 x N = 256, one N half after the
-//                      other) through a 5-slot ring tracked by full/empty mbarriers -- it starts at kernel entry, so the stream from L2 runs
-//                      under the gather, layer 1 and its epilogue and never waits for anything but a free slot
-//   warp 9 (one lane)  MMA issuer (and TMEM owner): 4 x tcgen05.mma for layer 1 (all 512 TMEM columns), then 2 per slab for layer 2;
-//                      tcgen05.commit frees ring slots and signals "N half 0 done" / "N half 1 done"
-//   warps 0-7          gather + epilogues; warp w reads TMEM lanes 32 (w % 4) .., the two warps of a lane quarter split the columns
+//   warp 8  producer: W1 (32 KB, one bulk TMA copy) and then W2 as 32 slabs of 16 KB (K = 32 x N = 256, one N half after the other) through a
+//           5-slot ring tracked by full/empty mbarriers -- it starts at kernel entry, so the stream from L2 runs under the gather, layer 1 and
+//           its epilogue and never waits for anything but a free slot.  Each CTA walks the K slabs from its own offset (blockIdx & 15).
+//   warp 9  MMA issuer (and TMEM owner): 4 x tcgen05.mma for layer 1 (all 512 TMEM columns), then 2 per slab for layer 2, all from ONE elected
+//           lane running the whole (unrolled) loop; tcgen05.commit frees ring slots and signals "N half 0 done" / "N half 1 done".
+//           (Issued from an `if (lane == 0)` region instead, every tcgen05 / TMA instruction is wrapped by the compiler in a waterfall loop
+//           of R2UR moves, and the tensor pipe idles half of the time.)
+//   warps 0-7  gather + epilogues; warp w reads TMEM lanes 32 (w % 4) .., the two warps of a lane quarter split the columns
 //     gather    : thread r < 128 rounds its environment's 17 scaled observations (parked list or direct rows) to bf16 and stores them as the
-//                 layer-1 A operand (K padded to 32) in the UMMA canonical K-major no-swizzle layout
-//     epilogue 1: tcgen05.ld, + b1, ReLU, bf16, written straight back to shared memory as the layer-2 A operand (128 KB, canonical layout;
-//                 W1 and the layer-1 A operand lived in the same bytes)
-//     epilogue 2: N half 0 (columns 0-255) is reduced while the tensor core works on N half 1: + b2, ReLU in fp32, the 512 -> 2 output
-//                 layer as two fp32 dot products per thread; then half 1, tanh, and the two actions go straight into the environment
+//                 layer-1 A operand (K padded to 32) in the UMMA canonical K-major no-swizzle layout; k = 17, 18 hold 1.0 and meet the two
+//                 bf16 pieces (hi + lo) of b1 that the host packed into W1's padding rows, so layer 1 needs no bias pass
+//     epilogue 1: tcgen05.ld (two 32-column chunks in flight), ReLU + bf16 in one cvt.rn.relu.bf16x2.f32 per pair, written straight back to
+//                 shared memory as the layer-2 A operand (128 KB, canonical layout; W1 and the layer-1 A operand lived in the same bytes);
+//                 the drained TMEM columns are refilled with b2 (tcgen05.st), so layer 2 accumulates on top of its bias
+//     epilogue 2: N half 0 (columns 0-255) is reduced while the tensor core works on N half 1: ReLU in fp32, the 512 -> 2 output layer as
+//                 packed fma.rn.f32x2 dot products per thread; then half 1, tanh, and the two actions go straight into the environment
 //                 record (policy_act, parked = 2) that the step kernel turns into the steering-rate / boggie-torque setpoints
 //                 (src/rover_1_tf.cc:184-185).
+// Where the time goes (tools/policy_tc_timeline.cu, 16384 rows, clk per CTA of 17950): prologue to layer-1 done 2850, epilogue 1 2400
+// (shared-memory bound: 128 KB of A-operand stores + the b2 reads), layer 2 10400 = 162 clk per 128x256x16 MMA where the tensor pipe needs
+// 128: the limit is the SM's shared-memory port -- per MMA 4 KB of A and 8 KB of B are read and 8 KB of the next slab are written by TMA,
+// 20 KB at 128 B/clk = 160 clk (W2 is always there before it is needed: L2 runs at 18 % of its rate) --, tail 2100.  Only cta_group::2
+// (each CTA of a pair holds half of B) goes below that; not built.  11.8 us per launch = 755 TFLOP/s, 53 % of the sustained bf16 rate of
+// this GPU (profiles/r02_policy_bench.txt, r02_ncu_policy_tc_kernel.md).
 // Operand layout (bf16, "core matrix" = 8 rows x 16 bytes, stored as 128 contiguous bytes):
 //   element (row, k) of an operand with R rows lives at  (k/8) * (R/8)*128 + (row/8)*128 + (row%8)*16 + (k%8)*2
 //   => stride-dimension byte offset (next 8 rows) = 128, leading-dimension byte offset (next 8 k) = R*16.
@@ -77,6 +87,12 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }   // the eight gather / epilogue warps
+// non-blocking phase test (mbarrier.try_wait may park the thread; this one never does)
+__device__ __forceinline__ uint32_t mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+  return ok;
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
@@ -86,27 +102,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "bra WAIT_%=;\n\t"
       "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
-// Developer experiment (TFODE_TC_EXP_SLEEPY): a whole warp waits, one lane polls with a suspend-time hint instead of every thread re-reading
-// the barrier word in a tight loop.
-__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
-#ifdef TFODE_TC_EXP_SLEEPY   // measured: wakes ~150 clk later than the plain poll and the MMAs run no faster -- polling is not what slows them
-  if ((threadIdx.x & 31) == 0) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAITW_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"
-        "@p bra DONEW_%=;\n\t"
-        "bra WAITW_%=;\n\t"
-        "DONEW_%=:\n\t}" ::"r"(bar), "r"(parity), "r"(20000u) : "memory");
-  }
-  __syncwarp();
-#else
-  mbar_wait(bar, parity);
-#endif
-}
 // 1-D bulk TMA copy global -> shared, completion counted in bytes on an mbarrier
 __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// One lane of a converged warp.  The warp-wide roles below (producer, MMA issuer) run their loops with all 32 lanes and elect a lane only around
+// the tcgen05 / TMA instructions: those take their operands from the uniform datapath, and issued from inside an `if (lane == 0)` region the
+// compiler wraps every one of them in a waterfall loop of R2UR moves (measured: the tensor pipe idle half of the time).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -193,8 +199,21 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 __device__ long long g_tc_timeline[2048 * 16];
 __device__ long long g_tc_slabs[64 * 4];   // CTA 0: per slab {TMA issued, full-wait begins, full-wait ends, MMAs issued}
 #define TC_MARK(i) (g_tc_timeline[(blockIdx.x & 2047) * 16 + (i)] = clock64())
-#define TC_SLAB_MARK(s, j) do { if (blockIdx.x == 0) g_tc_slabs[(s) * 4 + (j)] = clock64(); } while (0)
+#define TC_SLAB_MARK(s, j) ((void)0)
+__device__ unsigned g_tc_loop[32 * 8];     // CTA 0: clock() inside the MMA issue loop, per slab
+#ifdef TFODE_TC_LOOPMARKS   // five clock reads per slab: they cost about 80 clk of the 330 they measure
+#define TC_LOOP_DECL __shared__ unsigned tc_loop_sm[32 * 8];
+#define TC_LMARK(s, j) (tc_loop_sm[(s) * 8 + (j)] = (unsigned)clock())
+#define TC_LOOP_FLUSH do { if (blockIdx.x == 0) for (int i_ = threadIdx.x & 31; i_ < 32 * 8; i_ += 32) g_tc_loop[i_] = tc_loop_sm[i_]; } while (0)
 #else
+#define TC_LOOP_DECL
+#define TC_LMARK(s, j) ((void)0)
+#define TC_LOOP_FLUSH ((void)0)
+#endif
+#else
+#define TC_LOOP_DECL
+#define TC_LMARK(s, j) ((void)0)
+#define TC_LOOP_FLUSH ((void)0)
 #define TC_MARK(i) ((void)0)
 #define TC_SLAB_MARK(s, j) ((void)0)
 #endif
@@ -241,73 +260,81 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
 
   if (warp == 8) {
     // ---- producer: W1, then the 32 W2 slabs through the ring
-    if (lane == 0) {
+    if (elect_one()) {
       mbar_expect_tx(barW1, TC_W1_BYTES);
       tma_bulk_g2s(sW1, w1c, TC_W1_BYTES, barW1);
+    }
+    __syncwarp();
+    int slot = 0; uint32_t phase = 1;            // parity of the "slot is free" phase the producer waits for; nothing to wait for in round 0
 #pragma unroll 1
-      for (int s = 0; s < TC_NSLAB; s++) {
-        const int slot = s % TC_NSLOT, round = s / TC_NSLOT;
-        if (round > 0) mbar_wait(barEmpty + 8 * slot, (uint32_t)(round - 1) & 1u);
-        mbar_expect_tx(barFull + 8 * slot, TC_SLAB_BYTES);
-        const int gslab = (s & 16) | ((s + k0) & 15);   // N half, rotated K slab
+    for (int s = 0; s < TC_NSLAB; s++) {
+      if (s >= TC_NSLOT) mbar_wait(barEmpty + 8 * slot, phase);
+      const int gslab = (s & 16) | ((s + k0) & 15);   // N half, rotated K slab
+      if (elect_one()) {
         TC_SLAB_MARK(s, 0);
+        mbar_expect_tx(barFull + 8 * slot, TC_SLAB_BYTES);
         tma_bulk_g2s(sRing + slot * TC_SLAB_BYTES, reinterpret_cast<const uint8_t*>(w2c) + (size_t)gslab * TC_SLAB_BYTES, TC_SLAB_BYTES, barFull + 8 * slot);
       }
-      TC_MARK(11);
+      __syncwarp();
+      if (++slot == TC_NSLOT) { slot = 0; phase ^= 1u; }
     }
+    if (lane == 0) TC_MARK(11);
   } else if (warp == 9) {
     // ---- MMA issuer
-    if (lane == 0) {
-      mbar_wait(barW1, 0);
-      mbar_wait(barA1, 0);
-      tc_fence_after();
-      TC_MARK(2);
-      // layer 1: H1 = X(128x32) . W1^T, N in two halves of 256 columns
+    mbar_wait(barW1, 0);
+    mbar_wait(barA1, 0);
+    tc_fence_after();
+    if (lane == 0) TC_MARK(2);
+    // layer 1: H1 = X(128x32) . W1^T, N in two halves of 256 columns
+    {
+      const uint64_t ad0 = make_desc(sA1, TC_ROWS * 16, 128), bd0 = make_desc(sW1, TC_H * 16, 128);
+      if (elect_one()) {
 #pragma unroll
-      for (int ks = 0; ks < TC_K1 / 16; ks++)
+        for (int ks = 0; ks < TC_K1 / 16; ks++)
 #pragma unroll
-        for (int h = 0; h < 2; h++) {
-          const uint64_t ad = make_desc(sA1 + ks * 2 * (TC_ROWS * 16), TC_ROWS * 16, 128);
-          const uint64_t bd = make_desc(sW1 + ks * 2 * (TC_H * 16) + h * (256 / 8) * 128, TC_H * 16, 128);
-          mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, ks > 0);
-        }
-      mma_commit(barL1);
-      // layer 2: H2 = relu(H1)(128x512) . W2^T; N half 0 over all of K, then N half 1
-      mbar_wait(barA2, 0);
-      tc_fence_after();
-      TC_MARK(3);
-#pragma unroll 1
+          for (int h = 0; h < 2; h++)
+            mma_bf16(tmem + h * 256, ad0 + (uint64_t)((ks * 2 * (TC_ROWS * 16)) >> 4), bd0 + (uint64_t)((ks * 2 * (TC_H * 16) + h * (256 / 8) * 128) >> 4), IDESC_128x256, ks > 0);
+        mma_commit(barL1);
+      }
+      __syncwarp();
+    }
+    // layer 2: H2 = relu(H1)(128x512) . W2^T; N half 0 over all of K, then N half 1
+    mbar_wait(barA2, 0);
+    tc_fence_after();
+    if (lane == 0) TC_MARK(3);
+    const uint64_t ad0 = make_desc(sA2, TC_ROWS * 16, 128), bd0 = make_desc(sRing, TC_SLAB_N * 16, 128);
+    // No tcgen05.fence in this loop: the slab's bytes reach the MMA through the mbarrier (TMA complete_tx -> wait -> MMA, all in the async proxy).
+    // The whole loop runs in ONE elected lane: per slab it is a barrier poll, two MMA issues and a commit, ~50 clk of issue latency each, and
+    // they have to stay under the 2 x 128 clk the tensor pipe needs for the slab.  Electing a lane per slab (and reconverging the warp after it)
+    // cost another ~200 clk per slab and left the pipe idle a third of the time (tools/policy_tc_timeline.cu).
+    TC_LOOP_DECL
+    if (elect_one()) {
+      // Fully unrolled: slot, phase and N half are literals, and the barrier test of slab s+1 is issued before the MMAs of slab s so that its
+      // shared-memory round trip (56 clk) is off the issue path.
+      uint32_t ready = mbar_test(barFull, 0);
+#pragma unroll
       for (int s = 0; s < TC_NSLAB; s++) {
-        const int slot = s % TC_NSLOT, round = s / TC_NSLOT;
-        const int h = s >> 4, kslab = (s + k0) & 15;
-        TC_SLAB_MARK(s, 1);
-#ifndef TFODE_TC_EXP_NOWAIT   // developer experiment: raw MMA issue rate, operands = whatever the ring holds
-        mbar_wait(barFull + 8 * slot, (uint32_t)round & 1u);
-#endif
-        TC_SLAB_MARK(s, 2);
-#ifndef TFODE_TC_EXP_NOFENCE
-        tc_fence_after();
-#endif
-        if (s == 0) TC_MARK(13);
-        if (s == TC_NSLAB / 2 - 1) TC_MARK(12);
-        if (s == TC_NSLAB - 1) TC_MARK(4);
+        const int slot = s % TC_NSLOT, h = s >> 4, kslab = (s + k0) & 15;
+        const uint32_t phase = (uint32_t)(s / TC_NSLOT) & 1u;
+        TC_LMARK(s, 0);
+        if (!ready) mbar_wait(barFull + 8 * slot, phase);   // the slab's bytes reach the MMA through the mbarrier (TMA complete_tx -> wait -> MMA, all in the async proxy)
+        if (s + 1 < TC_NSLAB) ready = mbar_test(barFull + 8 * ((s + 1) % TC_NSLOT), (uint32_t)((s + 1) / TC_NSLOT) & 1u);
+        TC_LMARK(s, 1);
+        const uint64_t ad = ad0 + (uint64_t)(kslab * ((TC_SLAB_K / 8) * (TC_ROWS * 16) >> 4));
+        const uint64_t bd = bd0 + (uint64_t)(slot * (TC_SLAB_BYTES >> 4));
 #pragma unroll
-        for (int ks = 0; ks < TC_SLAB_K / 16; ks++) {
-#ifdef TFODE_TC_EXP_LAYOUT   // developer experiment (with TFODE_TC_EXP_NOWAIT; results are garbage): raw MMA rate with a swizzled operand layout type
-          const uint64_t ad = (make_desc(sA2 + (kslab & 7) * 16384 + ks * 32, 16, 1024) & ~(7ull << 61)) | ((uint64_t)TFODE_TC_EXP_LAYOUT << 61);
-          const uint64_t bd = (make_desc(sRing + ks * 32, 16, 1024) & ~(7ull << 61)) | ((uint64_t)TFODE_TC_EXP_LAYOUT << 61);
-#else
-          const uint64_t ad = make_desc(sA2 + (kslab * (TC_SLAB_K / 8) + ks * 2) * (TC_ROWS * 16), TC_ROWS * 16, 128);
-          const uint64_t bd = make_desc(sRing + slot * TC_SLAB_BYTES + ks * 2 * (TC_SLAB_N * 16), TC_SLAB_N * 16, 128);
-#endif
-          mma_bf16(tmem + h * 256, ad, bd, IDESC_128x256, 1u);   // the accumulators start from b2 (epilogue 1 put it there)
+        for (int ks = 0; ks < TC_SLAB_K / 16; ks++) {  // the accumulators start from b2 (epilogue 1 put it there): always accumulate
+          mma_bf16(tmem + h * 256, ad + (uint64_t)(ks * (2 * (TC_ROWS * 16) >> 4)), bd + (uint64_t)(ks * (2 * (TC_SLAB_N * 16) >> 4)), IDESC_128x256, 1u);
+          TC_LMARK(s, 3 + ks);
         }
         mma_commit(barEmpty + 8 * slot);       // arrives when the MMAs above have finished reading the slot
-        TC_SLAB_MARK(s, 3);
-        if (s == TC_NSLAB / 2 - 1) mma_commit(barH0);
+        if (s == TC_NSLAB / 2 - 1) { mma_commit(barH0); TC_MARK(12); }
+        if (s == TC_NSLAB - 1) { mma_commit(barH1); TC_MARK(4); }
+        TC_LMARK(s, 5);
       }
-      mma_commit(barH1);
     }
+    __syncwarp();
+    TC_LOOP_FLUSH;
   } else {
     // ---- gather and epilogues: lane quarter q = TMEM lanes 32 q .., column group g
     const int q = warp & 3, g = warp >> 2;
@@ -336,7 +363,7 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 
     // ---- epilogue 1: ReLU + bf16 (b1 came in through the MMA), written as the layer-2 A operand; group g takes columns [256 g, 256 g + 256)
-    mbar_wait_warp(barL1, 0);
+    mbar_wait(barL1, 0);
     tc_fence_after();
     if (t == 0) TC_MARK(5);
 #pragma unroll 1
@@ -374,7 +401,7 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
     uint64_t acc0 = 0ull, acc1 = 0ull;   // (even columns, odd columns) partial sums of output 0 / output 1
 #pragma unroll 1
     for (int half = 0; half < 2; half++) {
-      mbar_wait_warp(half ? barH1 : barH0, 0);
+      mbar_wait(half ? barH1 : barH0, 0);
       tc_fence_after();
       if (t == 0) TC_MARK(half ? 9 : 7);
       const int c0 = half * 8 + g * 4;

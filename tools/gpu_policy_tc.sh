@@ -4,7 +4,4 @@ mkdir -p gpurun_out
 timeout 300 python -m pytest tests/test_gpu_parity.py tests/test_gpu_configs.py -m gpu -q -k "policy_tc or tc_actor" > gpurun_out/pytest_policy_tc.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_policy_tc.log
 timeout 120 python tools/policy_bench.py 16384 > gpurun_out/policy_bench.log 2>&1; echo "bench rc=$?"; cat gpurun_out/policy_bench.log | cut -c1-250
 timeout 120 python tools/policy_bench.py 131072 > gpurun_out/policy_bench_131072.log 2>&1; cut -c1-120 gpurun_out/policy_bench_131072.log
-for v in base spin nowait; do for m in 128 16384; do
-  [ -x tools/policy_tc_timeline_$v ] || continue
-  timeout 60 tools/policy_tc_timeline_$v $m > gpurun_out/tl_${v}_$m.txt 2>&1; echo "== $v rows $m"; head -1 gpurun_out/tl_${v}_$m.txt; grep -A15 "mean over" gpurun_out/tl_${v}_$m.txt | tr -s ' ' | paste -sd' ' | cut -c1-600
-done; done
+bash tools/gpu_policy_tl.sh

@@ -47,11 +47,14 @@ int main(int argc, char** argv) {
     for (int k = 0; k < 14; k++) printf("  %-22s %7lld clk\n", names[order[k]], tl[b * 16 + order[k]] - tl[b * 16]);
   }
   {
-    static long long sl[64 * 4];
-    cudaMemcpyFromSymbol(sl, g_tc_slabs, sizeof(sl));
-    printf("CTA 0, per W2 slab (clk after entry): TMA issued | full-wait begins | ends (waited) | MMAs + commit issued\n");
-    for (int k = 0; k < TC_NSLAB; k++)
-      printf("  slab %2d  %7lld | %7lld | %7lld (%5lld) | %7lld\n", k, sl[k * 4] - tl[0], sl[k * 4 + 1] - tl[0], sl[k * 4 + 2] - tl[0], sl[k * 4 + 2] - sl[k * 4 + 1], sl[k * 4 + 3] - tl[0]);
+    static unsigned lp[32 * 8];
+    cudaMemcpyFromSymbol(lp, g_tc_loop, sizeof(lp));
+    printf("CTA 0, MMA issue loop, per W2 slab (clk since the previous slab's loop top): loop top | wait done | - | MMA 1 issued | MMA 2 issued | commit issued\n");
+    for (int k = 1; k < TC_NSLAB; k++) {
+      printf("  slab %2d  +%4u |", k, lp[k * 8] - lp[(k - 1) * 8]);
+      for (int j = 1; j < 6; j++) printf(" %5d", (int)(lp[k * 8 + j] - lp[k * 8]));
+      printf("\n");
+    }
   }
   double avg[16] = {0};
   const int nb = blocks < 2048 ? blocks : 2048;
