@@ -224,28 +224,47 @@ def verify_against_oracle(g, workload, n_envs, first, substeps, warmup, steps, i
 
 def actor_tc_line(peaks):
     """The batched tensor-core actor (policy_tc_kernel: tcgen05 / TMEM / bulk-TMA) on 16384 rows through tfode_policy_infer, timed with
-    CUDA events; tensor-pipe roofline against the measured bf16 peak."""
+    CUDA events two ways: a CUDA graph of 50 launches replayed back to back (the kernel's rate: one ctypes call costs the host as much as
+    the kernel runs, so a Python loop of launches would time the host), and ONE launch bracketed by events (its latency, launch overhead
+    included).  Tensor-pipe roofline of the first against the measured bf16 peak."""
     import numpy as np
     import torch
     from tf_ode_b200 import RoverBatch, abi, glorot_policy, make_config
-    rows = 16384
-    g = RoverBatch(make_config(abi.PRESET_TRAINING, 8, policy_precision=abi.POLICY_TC), stream=torch.cuda.current_stream().cuda_stream)
-    g.load_policy(glorot_policy())
-    x = torch.from_numpy(np.random.RandomState(3).rand(rows, 17).astype(np.float32) * 2 - 1).cuda()
-    y = torch.zeros(rows, 2, device="cuda")
-    for _ in range(5):
-        g.policy_infer(x, y)
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
-    for a, b in ev:
-        a.record(); g.policy_infer(x, y); b.record()
-    torch.cuda.synchronize()
-    us = sorted(a.elapsed_time(b) * 1e3 for a, b in ev)
-    med = us[len(us) // 2]
+    rows, per_graph, replays = 16384, 50, 40
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        g = RoverBatch(make_config(abi.PRESET_TRAINING, 8, policy_precision=abi.POLICY_TC), stream=side.cuda_stream)
+        g.load_policy(glorot_policy())
+        x = torch.from_numpy(np.random.RandomState(3).rand(rows, 17).astype(np.float32) * 2 - 1).cuda()
+        y = torch.zeros(rows, 2, device="cuda")
+        for _ in range(5):
+            g.policy_infer(x, y)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(20)]
+        for a, b in ev:
+            a.record(side); g.policy_infer(x, y); b.record(side)
+        side.synchronize()
+        single = sorted(a.elapsed_time(b) * 1e3 for a, b in ev)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            for _ in range(per_graph):
+                g.policy_infer(x, y)
+        graph.replay(); side.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(side)
+        for _ in range(replays):
+            graph.replay()
+        b.record(side)
+        side.synchronize()
+        us = a.elapsed_time(b) * 1e3 / (replays * per_graph)
+        del graph
+        g.close()
     flops = 2.0 * rows * (32 * 512 + 512 * 512)   # the MMAs the kernel issues (layer 1 padded to K = 32) -- the 512 -> 2 output layer is CUDA-core work
     peak = float(peaks.get("bf16_tflops", 1668.0))
-    g.close()
-    return {"kernel": "tfode::policy_tc_kernel", "rows": rows, "us_per_launch_median": med, "us_per_launch_min": us[0], "tflops": flops / (med * 1e-6) / 1e12,
-            "roofline": {"bound": "tensor", "achieved": flops / (med * 1e-6) / 1e12, "peak": peak, "unit": "TFLOP/s", "frac": flops / (med * 1e-6) / 1e12 / peak,
+    tf = flops / (us * 1e-6) / 1e12
+    return {"kernel": "tfode::policy_tc_kernel", "rows": rows, "us_per_launch": us, "launches_timed": replays * per_graph,
+            "how": "CUDA graph of %d tfode_policy_infer launches replayed %d times back to back, one CUDA-event pair around all of them" % (per_graph, replays),
+            "us_single_launch_median": single[len(single) // 2], "us_single_launch_min": single[0], "tflops": tf,
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": peak, "unit": "TFLOP/s", "frac": tf / peak,
                          "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst: the kernel is timed alone)" if peaks else "fallback"},
             "note": "batched tfode_policy_infer; inside tfode_batch_step the fp32 actor runs fused in step_kernel (no parking), which is faster end to end"}
 
