@@ -206,8 +206,8 @@ def numpy_mlp_bf16(w, x):
 
 @pytest.mark.parametrize("m", [1, 7, 128, 129, 1000, 16384])
 def test_policy_tc_matches_bf16_reference(m):
-    """tcgen05 kernel vs numpy with the same operand rounding: the fp32 accumulation order differs (the kernel walks K in a rotated
-    order per CTA and adds the biases inside the accumulation), and a hidden activation that lands within an fp32 ulp of a bf16 rounding
+    """tcgen05 kernel vs numpy with the same operand rounding: the fp32 accumulation order differs (the kernel adds the biases inside
+    the tensor core's accumulation), and a hidden activation that lands within an fp32 ulp of a bf16 rounding
     boundary may round the other way (one bf16 ulp of one of 512 activations): <= 5e-4 on a tanh output;
     vs the fp64 MLP on unrounded weights the bf16 operands cost <= 3e-2 on a tanh output (stated tolerance of the
     TFODE_POLICY_TC path; the fp32 kernel stays the bit-exact parity path)."""
@@ -226,6 +226,27 @@ def test_policy_tc_matches_bf16_reference(m):
     y = yd.cpu().numpy()
     assert np.abs(y - numpy_mlp_bf16(w, x)).max() <= 5e-4
     assert np.abs(y - numpy_mlp(w, x)).max() <= 3e-2
+    g.close()
+
+
+def test_policy_tc_action_does_not_depend_on_the_batch_position():
+    """Every CTA of policy_tc_kernel walks W2 in the same order: the same observation gives the same bits wherever it sits in the batch,
+    and whatever the batch size."""
+    g = RoverBatch(make_config(abi.PRESET_TRAINING, 8, policy_precision=abi.POLICY_TC))
+    g.load_policy(glorot_policy())
+    rs = np.random.RandomState(11)
+    x = rs.rand(3000, 17).astype(np.float32) * 2 - 1
+    probe = x[5].copy()
+    for pos in (0, 127, 128, 1500, 2999):
+        x[pos] = probe
+    yd = torch.zeros(3000, 2, device="cuda")
+    g.policy_infer(torch.from_numpy(x).cuda(), yd)
+    y = yd.cpu().numpy()
+    for pos in (0, 127, 128, 1500, 2999):
+        assert np.array_equal(y[pos], y[5]), pos
+    y1 = torch.zeros(1, 2, device="cuda")
+    g.policy_infer(torch.from_numpy(probe[None]).cuda(), y1)
+    assert np.array_equal(y1.cpu().numpy()[0], y[5]) and np.abs(y[5]).max() > 1e-4
     g.close()
 
 

@@ -4,7 +4,7 @@
 // One CTA = 128 environments (the M of a 128xNx16 UMMA tile = the 128 TMEM lanes), ten warps in three roles:
 //   warp 8  producer: W1 (32 KB, one bulk TMA copy) and then W2 as 32 slabs of 16 KB (K = 32 x N = 256, one N half after the other) through a
 //           5-slot ring tracked by full/empty mbarriers -- it starts at kernel entry, so the stream from L2 runs under the gather, layer 1 and
-//           its epilogue and never waits for anything but a free slot.  Each CTA walks the K slabs from its own offset (blockIdx & 15).
+//           its epilogue and never waits for anything but a free slot.
 //   warp 9  MMA issuer (and TMEM owner): 4 x tcgen05.mma for layer 1 (all 512 TMEM columns), then 2 per slab for layer 2, all from ONE elected
 //           lane running the whole (unrolled) loop; tcgen05.commit frees ring slots and signals "N half 0 done" / "N half 1 done".
 //           (Issued from an `if (lane == 0)` region instead, every tcgen05 / TMA instruction is wrapped by the compiler in a waterfall loop
@@ -20,12 +20,12 @@
 //                 packed fma.rn.f32x2 dot products per thread; then half 1, tanh, and the two actions go straight into the environment
 //                 record (policy_act, parked = 2) that the step kernel turns into the steering-rate / boggie-torque setpoints
 //                 (src/rover_1_tf.cc:184-185).
-// Where the time goes (tools/policy_tc_timeline.cu, 16384 rows, clk per CTA of 17950): prologue to layer-1 done 2850, epilogue 1 2400
-// (shared-memory bound: 128 KB of A-operand stores + the b2 reads), layer 2 10400 = 162 clk per 128x256x16 MMA where the tensor pipe needs
-// 128: the limit is the SM's shared-memory port -- per MMA 4 KB of A and 8 KB of B are read and 8 KB of the next slab are written by TMA,
-// 20 KB at 128 B/clk = 160 clk (W2 is always there before it is needed: L2 runs at 18 % of its rate) --, tail 2100.  Only cta_group::2
-// (each CTA of a pair holds half of B) goes below that; not built.  11.8 us per launch = 755 TFLOP/s, 53 % of the sustained bf16 rate of
-// this GPU (profiles/r02_policy_bench.txt, r02_ncu_policy_tc_kernel.md).
+// Where the time goes (tools/policy_tc_timeline.cu, 16384 rows, clk per CTA of 14800): prologue to layer-1 done 2850, first half of epilogue 1
+// 1350, layer 2 8450 = 132 clk per 128x256x16 MMA, the tensor pipe's own rate (the second half of epilogue 1 and epilogue 2 of N half 0 run
+// under it), tail 2100.  Every CTA asks L2 for the same W2 slab at about the same time, and that is what L2 serves best: with the K order
+// rotated per CTA (tried against slice hot-spotting) the 128 streams ran into the L2 slices' ~6300 B/clk and layer 2 took 162 clk per MMA.
+// 10.0 us per launch = 890 TFLOP/s, 63 % of the sustained (53 % of the burst) bf16 rate of this GPU; 1086 TFLOP/s at 131072 rows
+// (profiles/r02_policy_bench.txt, r02_ncu_policy_tc_kernel.md).
 // Operand layout (bf16, "core matrix" = 8 rows x 16 bytes, stored as 128 contiguous bytes):
 //   element (row, k) of an operand with R rows lives at  (k/8) * (R/8)*128 + (row/8)*128 + (row%8)*16 + (k%8)*2
 //   => stride-dimension byte offset (next 8 rows) = 128, leading-dimension byte offset (next 8 k) = R*16.
@@ -62,8 +62,8 @@ constexpr int TC_OFF_RING = TC_OFF_A2 + TC_A2_BYTES;            // 5 slots of 16
 constexpr int TC_OFF_B2 = TC_OFF_RING + TC_NSLOT * TC_SLAB_BYTES;   // fp32 b2[512]
 constexpr int TC_OFF_W3 = TC_OFF_B2 + TC_H * 4;                 // fp32 W3 transposed: [2][512]
 constexpr int TC_OFF_PART = TC_OFF_W3 + TC_H * 2 * 4;           // fp32 partial output sums [128][2]
-constexpr int TC_OFF_BAR = TC_OFF_PART + TC_ROWS * 2 * 4;       // mbarriers: full[5], empty[5], W1, A1, L1, A2, H0, H1
-constexpr int TC_OFF_TMEM = TC_OFF_BAR + 16 * 8;
+constexpr int TC_OFF_BAR = TC_OFF_PART + TC_ROWS * 2 * 4;       // mbarriers: full[5], empty[5], W1, A1, L1, A2 (first half), H0, H1, A2 (second half)
+constexpr int TC_OFF_TMEM = TC_OFF_BAR + 18 * 8;
 constexpr int TC_SMEM_BYTES = TC_OFF_TMEM + 16;
 static_assert(TC_A1_BYTES + TC_W1_BYTES <= TC_A2_BYTES && TC_SMEM_BYTES <= 227 * 1024, "shared memory map");
 
@@ -233,7 +233,7 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
 
   const uint32_t sA2 = smem_u32(smem + TC_OFF_A2), sRing = smem_u32(smem + TC_OFF_RING), sA1 = smem_u32(smem + TC_OFF_A1), sW1 = smem_u32(smem + TC_OFF_W1);
   const uint32_t barFull = smem_u32(smem + TC_OFF_BAR), barEmpty = barFull + 8 * TC_NSLOT, barW1 = barFull + 80, barA1 = barFull + 88, barL1 = barFull + 96,
-                 barA2 = barFull + 104, barH0 = barFull + 112, barH1 = barFull + 120;
+                 barA2 = barFull + 104, barH0 = barFull + 112, barH1 = barFull + 120, barA2b = barFull + 128;
   float* sb2 = reinterpret_cast<float*>(smem + TC_OFF_B2);
   float* sW3 = reinterpret_cast<float*>(smem + TC_OFF_W3);
   float* sPart = reinterpret_cast<float*>(smem + TC_OFF_PART);
@@ -241,7 +241,7 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
 
   if (t == 0) {
     for (int i = 0; i < TC_NSLOT; i++) { mbar_init(barFull + 8 * i, 1); mbar_init(barEmpty + 8 * i, 1); }
-    mbar_init(barW1, 1); mbar_init(barA1, TC_ROWS); mbar_init(barL1, 1); mbar_init(barA2, 256); mbar_init(barH0, 1); mbar_init(barH1, 1);
+    mbar_init(barW1, 1); mbar_init(barA1, TC_ROWS); mbar_init(barL1, 1); mbar_init(barA2, 256); mbar_init(barA2b, 256); mbar_init(barH0, 1); mbar_init(barH1, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 9) {  // one warp owns the TMEM allocation (all 512 columns: 128 lanes x 512 fp32 accumulators)
@@ -253,10 +253,6 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   if (t == 0) TC_MARK(1);
-  // The CTAs of a launch run in step and W2 is the same 512 KB for all of them: started on the same slab they would all pull the same
-  // 16 KB out of the same few L2 slices at the same moment (measured: 30 B/clk per SM).  Each CTA therefore walks the 16 K slabs of an
-  // N half from its own offset; the sum over K is the same set of products, accumulated in a rotated order.
-  const int k0 = blockIdx.x & 15;
 
   if (warp == 8) {
     // ---- producer: W1, then the 32 W2 slabs through the ring
@@ -269,7 +265,9 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
 #pragma unroll 1
     for (int s = 0; s < TC_NSLAB; s++) {
       if (s >= TC_NSLOT) mbar_wait(barEmpty + 8 * slot, phase);
-      const int gslab = (s & 16) | ((s + k0) & 15);   // N half, rotated K slab
+      const int gslab = s;                            // slabs 0-15: N half 0, K ascending; 16-31: N half 1 (every CTA in the same order: a row's
+                                                      // action does not depend on where in the batch it sits; a per-CTA rotation was tried against
+                                                      // L2 hot-spotting and changed nothing)
       if (elect_one()) {
         TC_SLAB_MARK(s, 0);
         mbar_expect_tx(barFull + 8 * slot, TC_SLAB_BYTES);
@@ -298,7 +296,8 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
       }
       __syncwarp();
     }
-    // layer 2: H2 = relu(H1)(128x512) . W2^T; N half 0 over all of K, then N half 1
+    // layer 2: H2 = relu(H1)(128x512) . W2^T; N half 0 over all of K, then N half 1.  It starts when epilogue 1 is through columns 0-255 (the
+    // first 8 K slabs of the A operand, and the accumulator columns of N half 0); the other half of epilogue 1 runs under those 16 MMAs.
     mbar_wait(barA2, 0);
     tc_fence_after();
     if (lane == 0) TC_MARK(3);
@@ -314,9 +313,10 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
       uint32_t ready = mbar_test(barFull, 0);
 #pragma unroll
       for (int s = 0; s < TC_NSLAB; s++) {
-        const int slot = s % TC_NSLOT, h = s >> 4, kslab = (s + k0) & 15;
+        const int slot = s % TC_NSLOT, h = s >> 4, kslab = s & 15;
         const uint32_t phase = (uint32_t)(s / TC_NSLOT) & 1u;
         TC_LMARK(s, 0);
+        if (s == 8) { mbar_wait(barA2b, 0); tc_fence_after(); }   // K >= 256 of the A operand and the accumulator columns of N half 1
         if (!ready) mbar_wait(barFull + 8 * slot, phase);   // the slab's bytes reach the MMA through the mbarrier (TMA complete_tx -> wait -> MMA, all in the async proxy)
         if (s + 1 < TC_NSLAB) ready = mbar_test(barFull + 8 * ((s + 1) % TC_NSLOT), (uint32_t)((s + 1) / TC_NSLOT) & 1u);
         TC_LMARK(s, 1);
@@ -362,13 +362,20 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
     epi_bar_sync();
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
 
-    // ---- epilogue 1: ReLU + bf16 (b1 came in through the MMA), written as the layer-2 A operand; group g takes columns [256 g, 256 g + 256)
+    // ---- epilogue 1: ReLU + bf16 (b1 came in through the MMA), written as the layer-2 A operand; columns 0-255 first (group g takes 128 of
+    //      them), hand-over to the MMA warp, then columns 256-511
     mbar_wait(barL1, 0);
     tc_fence_after();
     if (t == 0) TC_MARK(5);
 #pragma unroll 1
-    for (int ci = 0; ci < 8; ci += 2) {          // two chunks of 32 columns in flight per round trip to TMEM
-      const int c = g * 8 + ci;
+    for (int ci = 0; ci < 8; ci += 2) {          // two chunks of 32 columns in flight per round trip to TMEM (four at once measured slower)
+      const int c = (ci >> 2) * 8 + g * 4 + (ci & 3);
+      if (ci == 4) {                              // columns 0-255 are drained, refilled with b2 and in shared memory as bf16: layer 2 may start
+        tmem_wait_st();
+        fence_proxy_async();
+        tc_fence_before();
+        mbar_arrive(barA2);
+      }
       uint32_t v[2][32], bias[2][32];
       tmem_ld32_issue(lane_base + c * 32, v[0]);
       tmem_ld32_issue(lane_base + c * 32 + 32, v[1]);
@@ -394,7 +401,7 @@ policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list,
     tmem_wait_st();
     fence_proxy_async();
     tc_fence_before();       // the tcgen05.ld reads of H1 are ordered before the MMAs that overwrite those columns
-    mbar_arrive(barA2);
+    mbar_arrive(barA2b);
     if (t == 0) TC_MARK(6);
 
     // ---- epilogue 2: ReLU (b2 was the accumulators' start value), output layer 512 -> 2 in fp32; N half 0 while half 1 is in the tensor pipe, group g takes 128 columns of each
