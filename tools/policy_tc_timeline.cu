@@ -37,15 +37,16 @@ int main(int argc, char** argv) {
   static long long tl[2048 * 16];
   cudaMemcpyFromSymbol(tl, g_tc_timeline, sizeof(tl));
   const int blocks = (m + TC_ROWS - 1) / TC_ROWS;
-  const char* names[16] = {"entry", "setup done", "W1+A1 ready", "A2 ready (L2 start)", "last slab arrived", "L1 done", "epi1 done", "H0 done", "epi2 done", "H1 done", "end", "producer done", "slab 15 arrived", "slab 0 arrived", "", ""};
-  const int order[14] = {0, 1, 2, 5, 6, 3, 13, 12, 7, 11, 4, 9, 8, 10};
+  const char* names[16] = {"entry", "setup done", "W1+A1 ready", "A2 first half ready (L2 start)", "last slab arrived", "L1 done", "epi1 done", "H0 done", "epi2 done", "H1 done", "end", "producer done", "slab 15 arrived", "slab 0 arrived", "", ""};
+  const int order[13] = {0, 1, 2, 5, 3, 6, 12, 7, 11, 4, 9, 8, 10};
   long long t0min = tl[0];
   for (int b = 0; b < blocks && b < 2048; b++) if (tl[b * 16] < t0min) t0min = tl[b * 16];
   for (int b : {0, 1, blocks / 2, blocks - 1}) {
     if (b < 0 || b >= 2048) continue;
     printf("CTA %d (entry at +%lld clk after the first CTA's entry; clock64 is per SM, compare within a CTA):\n", b, tl[b * 16] - t0min);
-    for (int k = 0; k < 14; k++) printf("  %-22s %7lld clk\n", names[order[k]], tl[b * 16 + order[k]] - tl[b * 16]);
+    for (int k = 0; k < 13; k++) printf("  %-22s %7lld clk\n", names[order[k]], tl[b * 16 + order[k]] - tl[b * 16]);
   }
+#ifdef TFODE_TC_LOOPMARKS
   {
     static unsigned lp[32 * 8];
     cudaMemcpyFromSymbol(lp, g_tc_loop, sizeof(lp));
@@ -56,11 +57,12 @@ int main(int argc, char** argv) {
       printf("\n");
     }
   }
+#endif
   double avg[16] = {0};
   const int nb = blocks < 2048 ? blocks : 2048;
   for (int b = 0; b < nb; b++) for (int k = 0; k < 16; k++) avg[k] += (double)(tl[b * 16 + k] - tl[b * 16]) / nb;
   printf("mean over %d CTAs:\n", nb);
-  for (int k = 0; k < 14; k++) printf("  %-22s %9.0f clk\n", names[order[k]], avg[order[k]]);
+  for (int k = 0; k < 13; k++) printf("  %-22s %9.0f clk\n", names[order[k]], avg[order[k]]);
 #endif
   return 0;
 }
