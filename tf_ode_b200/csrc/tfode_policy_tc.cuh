@@ -218,7 +218,8 @@ __device__ unsigned g_tc_loop[32 * 8];     // CTA 0: clock() inside the MMA issu
 #define TC_SLAB_MARK(s, j) ((void)0)
 #endif
 
-// in_all: [*,17] scaled observations; list/n_list: parked environments (device) or nullptr for direct rows [0, m_direct)
+// in_all: [*,17] scaled observations; list/n_list: parked environments (device) or nullptr for direct rows [0, m_direct).
+// b1 is not read here: policy_tc_upload folds it into w1c (rows k = 17, 18); the parameter keeps the launch signature of the fp32 kernel.
 __global__ void __launch_bounds__(TC_THREADS, 1)
 policy_tc_kernel(const float* __restrict__ in_all, const int* __restrict__ list, const int* __restrict__ n_list, int m_direct,
                  const __nv_bfloat16* __restrict__ w1c, const __nv_bfloat16* __restrict__ w2c, const float* __restrict__ b1,
